@@ -1,0 +1,124 @@
+"""Seeded synthetic inputs of the shapes BASELINE.json names.
+
+All generators are numpy-only and deterministic for a given (size, seed).
+Sizes follow the reference CLI's legality rule: callers should use
+k*block + tail with tail >= 9 bytes.
+"""
+import numpy as np
+
+
+def markov_text(size, seed=42, order=2):
+    """Order-2 Markov text over 27 symbols (a-z, space), Dirichlet(0.15) rows."""
+    rng = np.random.default_rng(seed)
+    k = 27
+    alpha = np.frombuffer(b"abcdefghijklmnopqrstuvwxyz ", dtype=np.uint8)
+    rows = rng.dirichlet(np.full(k, 0.15), size=k * k)
+    cdf = np.cumsum(rows, axis=1)
+    u = rng.random(size)
+    out = np.empty(size, dtype=np.int64)
+    a = b = 0
+    for i in range(size):
+        c = int(np.searchsorted(cdf[a * k + b], u[i]))
+        if c >= k:
+            c = k - 1
+        out[i] = c
+        a, b = b, c
+    return alpha[out]
+
+
+def english_like(size, seed=1, vocab=4096, zipf_s=1.3):
+    """Zipf-distributed draws from a fixed vocabulary joined by spaces/punctuation."""
+    rng = np.random.default_rng(seed)
+    letters = np.frombuffer(b"etaoinshrdlcumwfgypbvkjxqz", dtype=np.uint8)
+    lw = 1.0 / np.arange(1, 27) ** 0.8
+    lw /= lw.sum()
+    wl = np.clip(rng.poisson(4.2, vocab) + 1, 1, 14)
+    words = [letters[rng.choice(26, size=int(l), p=lw)].tobytes() for l in wl]
+    pw = 1.0 / np.arange(1, vocab + 1) ** zipf_s
+    pw /= pw.sum()
+    # draw enough words for `size` bytes (mean word+sep ~ 6.5 bytes)
+    nw = int(size / 4.0) + 64
+    idx = rng.choice(vocab, size=nw, p=pw)
+    seps = rng.choice(np.array([0, 0, 0, 0, 0, 0, 0, 1, 2, 3]), size=nw)
+    septab = [b" ", b", ", b". ", b"\n"]
+    parts = []
+    total = 0
+    for w, s in zip(idx, seps):
+        t = words[w] + septab[s]
+        parts.append(t)
+        total += len(t)
+        if total >= size:
+            break
+    buf = b"".join(parts)
+    while len(buf) < size:
+        buf += buf[: size - len(buf)]
+    return np.frombuffer(buf[:size], dtype=np.uint8).copy()
+
+
+def dna_like(size, seed=2, block=1 << 20, repeats_per_block=3, kmin=6, kmax=19):
+    """Uniform ACGT background with planted repeats of length 2^k copied from
+    earlier positions of the same block (so they survive blocking)."""
+    rng = np.random.default_rng(seed)
+    out = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=size)].copy()
+    nblocks = (size + block - 1) // block
+    for b in range(nblocks):
+        lo = b * block
+        hi = min(size, lo + block)
+        span = hi - lo
+        for _ in range(repeats_per_block):
+            k = int(rng.integers(kmin, kmax + 1))
+            L = min(1 << k, span // 2 - 1)
+            if L < 16:
+                continue
+            src = int(rng.integers(0, span - 2 * L + 1))
+            dst = int(rng.integers(src + L, span - L + 1))
+            out[lo + dst: lo + dst + L] = out[lo + src: lo + src + L]
+    return out
+
+
+def single_byte(size, byte=0x61):
+    return np.full(size, byte, dtype=np.uint8)
+
+
+def uniform_random(size, seed=4):
+    return np.random.default_rng(seed).integers(0, 256, size=size, dtype=np.uint8)
+
+
+def mixed_stream(size, seed=3, section=8 << 20):
+    """Concatenation of english-like, dna-like and random sections (config 4)."""
+    out = np.empty(size, dtype=np.uint8)
+    pos = 0
+    k = 0
+    while pos < size:
+        ln = min(section, size - pos)
+        kind = k % 3
+        if kind == 0:
+            out[pos: pos + ln] = english_like(ln, seed=seed * 1000 + k)
+        elif kind == 1:
+            out[pos: pos + ln] = dna_like(ln, seed=seed * 1000 + k)
+        else:
+            out[pos: pos + ln] = uniform_random(ln, seed=seed * 1000 + k)
+        pos += ln
+        k += 1
+    return out
+
+
+def small_cases(seed=0):
+    """The five small-input kinds the survey used (Appendix B), 9..3000 bytes."""
+    rng = np.random.default_rng(seed)
+    cases = []
+    for i in range(8):
+        n = int(rng.integers(9, 3000))
+        cases.append(("binary%d" % i, rng.integers(0, 2, n).astype(np.uint8) + 97))
+        cases.append(("random%d" % i, rng.integers(0, 256, n).astype(np.uint8)))
+        cases.append(("single%d" % i, np.full(n, int(rng.integers(0, 256)), np.uint8)))
+        per = rng.integers(0, 256, int(rng.integers(1, 40))).astype(np.uint8)
+        cases.append(("periodic%d" % i, np.resize(per, n)))
+        base = rng.integers(0, 4, n).astype(np.uint8) + 65
+        if n > 64:
+            L = int(rng.integers(8, n // 3))
+            s = int(rng.integers(0, n - 2 * L))
+            d = int(rng.integers(s + L, n - L + 1))
+            base[d: d + L] = base[s: s + L]
+        cases.append(("planted%d" % i, base))
+    return cases
