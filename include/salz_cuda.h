@@ -1,0 +1,132 @@
+/*
+ * salz_cuda.h - C ABI of the B200-native salz compression hot path.
+ *
+ * Plain C: pointers and sizes only.  This is the boundary the host code
+ * (lib/salz.c, programs/salzcli.c, or any FFI) binds instead of the
+ * reference's per-block CPU encoder:
+ *
+ *   salz_cuda_encode_blocks  == a loop of salz_encode_safe   (ref lib/salz.c:777-823,
+ *                                                              API ref lib/salz.h:42-43)
+ *   salz_cuda_encode_stream  == the CLI block loop + framing  (ref programs/salzcli.c:143-179)
+ *   salz_cuda_debug_stages   == the intermediates of          (ref lib/salz.c:463-662)
+ *
+ * Every entry point runs hand-written sm_100a kernels; there is no CPU
+ * fallback.  Without a CUDA device ctx_create returns NULL and every other
+ * call fails with -1.
+ */
+#ifndef SALZ_CUDA_H
+#define SALZ_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct salz_cuda_ctx salz_cuda_ctx;
+
+/* Per-context counters, accumulated since ctx_create / stats_reset. */
+typedef struct salz_cuda_stats {
+    uint64_t blocks;          /* blocks encoded */
+    uint64_t input_bytes;     /* sum of block lengths */
+    uint64_t output_bytes;    /* sum of encoded lengths (block headers included) */
+    uint64_t launches;        /* kernels launched */
+    uint64_t sort_launches;   /* of which radix scatter passes */
+    uint64_t sort_elems;      /* elements moved by the scatter passes (sum over passes) */
+    uint64_t doubling_rounds; /* prefix-doubling rounds executed (sum over batches) */
+    uint64_t alg_bytes_sa;    /* algorithmic HBM bytes, suffix sorting */
+    uint64_t alg_bytes_rest;  /* algorithmic HBM bytes, LCP/ANSV/parse/emit */
+    double ms_sa;             /* CUDA-event time per stage, milliseconds */
+    double ms_sort;           /* of which inside the radix scatter passes */
+    double ms_lcp;
+    double ms_ansv;
+    double ms_parse;
+    double ms_emit;
+    double ms_total;          /* whole device pipeline (excludes H2D/D2H) */
+    double ms_h2d;
+    double ms_d2h;
+} salz_cuda_stats;
+
+/* Number of CUDA devices visible (0 when none / no driver). */
+int salz_cuda_device_count(void);
+
+/*
+ * Create a context on `device` with workspace for batches of up to
+ * `max_batch_blocks` blocks of up to `max_block_len` bytes each.
+ * (replaces encode_ctx_create's per-call calloc, ref lib/salz.c:175-247)
+ * Returns NULL on failure (no device, out of memory, bad arguments).
+ */
+salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
+                                    size_t max_batch_blocks);
+void salz_cuda_ctx_destroy(salz_cuda_ctx *ctx);
+
+/* Text of the last error on this context ("" if none). */
+const char *salz_cuda_last_error(const salz_cuda_ctx *ctx);
+
+/*
+ * Encode `nblocks` independent blocks held in host memory.
+ * For block i: srcs[i]/src_lens[i] in, dsts[i] out with capacity dst_lens[i]
+ * in and encoded length out, rcs[i] = 0 / -1 with salz_encode_safe's
+ * conventions (src_len <= 8, NULL buffers or insufficient capacity => -1,
+ * dst_lens[i] untouched on failure).  Output bytes are identical to the
+ * reference's.  Returns 0 if the batch ran (inspect rcs), -1 on a CUDA error.
+ */
+int salz_cuda_encode_blocks(salz_cuda_ctx *ctx, const uint8_t *const *srcs,
+                            const size_t *src_lens, uint8_t *const *dsts,
+                            size_t *dst_lens, int *rcs, size_t nblocks);
+
+/*
+ * Encode a contiguous host stream cut at `block_len` boundaries and write
+ * the CLI framing for every block: u32 encoded_len (native endian) followed
+ * by the encoded block (ref programs/salzcli.c:162-169).  The 8-byte file
+ * header is the caller's.  `block_sizes` (optional) receives the per-block
+ * encoded_len; `*nblocks` (optional) the block count.  Fails (-1) when any
+ * block is <= 8 bytes (the reference CLI fails on such files too) or when
+ * dst_cap is too small.
+ */
+int salz_cuda_encode_stream(salz_cuda_ctx *ctx, const uint8_t *src,
+                            size_t src_len, size_t block_len, uint8_t *dst,
+                            size_t dst_cap, size_t *dst_len,
+                            uint32_t *block_sizes, size_t *nblocks);
+
+/* Same, but `d_src` and `d_dst` are device pointers on the context's device
+ * (inputs already resident in HBM; used for kernel-only timing).
+ * block_sizes is a HOST array. */
+int salz_cuda_encode_stream_device(salz_cuda_ctx *ctx, const uint8_t *d_src,
+                                   size_t src_len, size_t block_len,
+                                   uint8_t *d_dst, size_t dst_cap,
+                                   size_t *dst_len, uint32_t *block_sizes,
+                                   size_t *nblocks);
+
+/*
+ * Test hook: run one block (N bytes, n = N - 8) and copy the intermediates
+ * to host arrays (any may be NULL):
+ *   sa[n]      suffix array of src[0..n)                 (ref lib/salz.c:463-469)
+ *   plcp[n], lcp[n]                                      (ref libsais.h:319,329)
+ *   cand[4n]   (p-psv, psv_len, p-nsv, nsv_len)          (ref lib/salz.c:540-560)
+ *   parse[3n]  (offs, len, cost) after the optimal parse (ref lib/salz.c:610-662)
+ *   dst/dst_len encoded block
+ */
+int salz_cuda_debug_stages(salz_cuda_ctx *ctx, const uint8_t *src, size_t N,
+                           int32_t *sa, int32_t *plcp, int32_t *lcp,
+                           int32_t *cand, int32_t *parse, uint8_t *dst,
+                           size_t *dst_len);
+
+/* Suffix arrays only, for a batch of texts laid out at `stride` bytes in one
+ * host buffer (SA-build GB/s measurements).  sa_out[i*stride + r]. */
+int salz_cuda_suffix_arrays(salz_cuda_ctx *ctx, const uint8_t *texts,
+                            const uint32_t *lens, size_t stride, size_t ntexts,
+                            int32_t *sa_out);
+
+int salz_cuda_get_stats(const salz_cuda_ctx *ctx, salz_cuda_stats *out);
+void salz_cuda_reset_stats(salz_cuda_ctx *ctx);
+
+/* Tunables (tests): mode 0 = two-kernel histogram + scatter, 1 = single-pass
+ * decoupled look-back scatter (default). */
+void salz_cuda_set_sort_mode(salz_cuda_ctx *ctx, int mode);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SALZ_CUDA_H */

@@ -1,0 +1,303 @@
+// emit.cu - token selection and bit/byte encoding with prefix-sum offsets.
+//
+// Replaces emit_encoding + finalize_encoding and the sequential writer
+// (ref lib/salz.c:258-457, 664-775) by the closed form of the stream layout:
+//
+//   token t (t-th token of the parse, the 8 tail literals included) emits
+//   pre-bits, one direct byte, post-bits:
+//     literal        pre = '0'                     byte = T[p]          post = -
+//     factor (o,l)   pre = '1' + vnibble((o-1)>>8) byte = (o-1)&0xff    post = GR3(l-3)
+//   B_t = bits emitted before token t.  Bit words are 64-bit, MSB first, stored
+//   little-endian, and each word's 8-byte slot is reserved when its first bit
+//   is produced, so
+//     word k  sits at  4 + 8k + y_k,  y_k = t   if bit 64k is a pre-bit of token t
+//                                           t+1 if it is a post-bit of token t
+//     byte of token t sits at  4 + t + 8*ceil((B_t + |pre_t|)/64)
+//   total = 4 + m + 8*ceil(B_m/64); PLAIN fallback when total > N + 4.
+//
+// Every output byte is written exactly once (bytes by their token, words by
+// one thread per word), so no zero-fill and no atomics are needed.
+#include "salz_dev.cuh"
+
+namespace {
+
+constexpr uint32_t NONE = 0xffffffffu;
+
+struct TokBits { int pre; int post; };
+
+__device__ __forceinline__ TokBits token_bits(int2 c)
+{
+    TokBits tb;
+    if (c.y == 1) { tb.pre = 1; tb.post = 0; }
+    else { tb.pre = factor_pre_bits((uint32_t)c.x); tb.post = factor_post_bits((uint32_t)c.y); }
+    return tb;
+}
+
+// One thread per block: follow the chunk-exit pointers from position 0.
+__global__ void k_chunk_entries(const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ jump, int logS,
+                                int B, uint32_t *__restrict__ chunkEntry)
+{
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const uint32_t N = blkN[b];
+    const size_t gb = (size_t)b << logS;
+    uint32_t *ce = chunkEntry + (gb >> PARSE_CHUNK_LOG);
+    uint32_t e = 0;
+    while (e < N) {
+        ce[e >> PARSE_CHUNK_LOG] = e;
+        e = jump[gb + e];
+    }
+}
+
+// One thread per chunk: count the tokens that start in the chunk and their bits.
+__global__ void __launch_bounds__(128) k_walk_count(const uint32_t *__restrict__ blkN,
+                                                    const int2 *__restrict__ choice,
+                                                    const uint32_t *__restrict__ chunkEntry, int logS,
+                                                    uint32_t totalChunks, uint32_t *__restrict__ chunkTok,
+                                                    uint32_t *__restrict__ chunkBits)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= totalChunks) return;
+    uint32_t e = chunkEntry[c];
+    uint32_t ntok = 0, nbits = 0;
+    if (e != NONE) {
+        const uint32_t b = c >> (logS - PARSE_CHUNK_LOG);
+        const uint32_t N = blkN[b];
+        const size_t gb = (size_t)b << logS;
+        const uint32_t end = min(N, ((e >> PARSE_CHUNK_LOG) + 1) << PARSE_CHUNK_LOG);
+        uint32_t p = e;
+        while (p < end) {
+            int2 ch = choice[gb + p];
+            TokBits tb = token_bits(ch);
+            ntok++;
+            nbits += tb.pre + tb.post;
+            p += (uint32_t)ch.y;
+        }
+    }
+    chunkTok[c] = ntok;
+    chunkBits[c] = nbits;
+}
+
+// One CTA per block: exclusive scan over its chunks; block totals and sizes.
+__global__ void __launch_bounds__(256) k_block_scan(const uint32_t *__restrict__ blkN, uint32_t chunksPerBlock,
+                                                    uint32_t *__restrict__ chunkTok, uint32_t *__restrict__ chunkBits,
+                                                    uint32_t *__restrict__ blkTokens, uint32_t *__restrict__ blkBits,
+                                                    uint32_t *__restrict__ blkSalzLen, uint32_t *__restrict__ blkOutLen)
+{
+    __shared__ uint32_t pt[256], pb[256];
+    const uint32_t b = blockIdx.x;
+    uint32_t *ct = chunkTok + (size_t)b * chunksPerBlock;
+    uint32_t *cb = chunkBits + (size_t)b * chunksPerBlock;
+    uint32_t per = (chunksPerBlock + 255) / 256;
+    uint32_t lo = threadIdx.x * per, hi = min(chunksPerBlock, lo + per);
+    uint32_t st = 0, sb = 0;
+    for (uint32_t i = lo; i < hi; i++) { st += ct[i]; sb += cb[i]; }
+    pt[threadIdx.x] = st;
+    pb[threadIdx.x] = sb;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t rt = 0, rb = 0;
+        for (int i = 0; i < 256; i++) {
+            uint32_t a = pt[i], c = pb[i];
+            pt[i] = rt; pb[i] = rb;
+            rt += a; rb += c;
+        }
+        const uint32_t N = blkN[b];
+        uint32_t salz = 4 + rt + 8 * ((rb + 63) / 64);
+        blkTokens[b] = rt;
+        blkBits[b] = rb;
+        blkSalzLen[b] = salz;
+        blkOutLen[b] = (salz > N + 4) ? (N + 4) : salz;
+    }
+    __syncthreads();
+    st = pt[threadIdx.x];
+    sb = pb[threadIdx.x];
+    for (uint32_t i = lo; i < hi; i++) {
+        uint32_t a = ct[i], c = cb[i];
+        ct[i] = st; cb[i] = sb;
+        st += a; sb += c;
+    }
+}
+
+// Offsets of the block records in the packed output stream.
+__global__ void k_out_offsets(const uint32_t *__restrict__ blkOutLen, int B, int framing,
+                              uint64_t *__restrict__ blkOutOff)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        uint64_t off = 0;
+        for (int b = 0; b < B; b++) {
+            blkOutOff[b] = off;
+            off += (uint64_t)blkOutLen[b] + (framing ? 4 : 0);
+        }
+        blkOutOff[B] = off;
+    }
+}
+
+// One thread per chunk: assign token indices and bit offsets, write the
+// direct bytes, record which token owns the first bit of every word.
+__global__ void __launch_bounds__(128) k_emit_tokens(
+    const uint8_t *__restrict__ T, size_t Tstride, const uint32_t *__restrict__ blkN,
+    const int2 *__restrict__ choice, const uint32_t *__restrict__ chunkEntry, const uint32_t *__restrict__ chunkTok,
+    const uint32_t *__restrict__ chunkBits, const uint32_t *__restrict__ blkSalzLen,
+    const uint64_t *__restrict__ blkOutOff, int framing, int logS, uint32_t totalChunks,
+    uint32_t *__restrict__ tokPos, uint32_t *__restrict__ tokBit, uint32_t *__restrict__ firstTok,
+    uint8_t *__restrict__ out)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= totalChunks) return;
+    uint32_t e = chunkEntry[c];
+    if (e == NONE) return;
+    const uint32_t b = c >> (logS - PARSE_CHUNK_LOG);
+    const uint32_t N = blkN[b];
+    if (blkSalzLen[b] > N + 4) return;  // PLAIN block
+    const size_t gb = (size_t)b << logS;
+    const uint8_t *Tb = T + (size_t)b * Tstride;
+    uint8_t *ob = out + blkOutOff[b] + (framing ? 4 : 0);
+    uint32_t *tp = tokPos + gb, *tbit = tokBit + gb;
+    uint32_t *ft = firstTok + (gb >> 2);
+    const uint32_t end = min(N, ((e >> PARSE_CHUNK_LOG) + 1) << PARSE_CHUNK_LOG);
+    uint32_t t = chunkTok[c], Bt = chunkBits[c];
+    uint32_t p = e;
+    while (p < end) {
+        int2 ch = choice[gb + p];
+        TokBits tb = token_bits(ch);
+        tp[t] = p;
+        tbit[t] = Bt;
+        uint32_t bytePos = 4 + t + 8 * ((Bt + tb.pre + 63) >> 6);
+        ob[bytePos] = (ch.y == 1) ? Tb[p] : (uint8_t)(((uint32_t)ch.x - 1u) & 0xffu);
+        uint32_t Bn = Bt + tb.pre + tb.post;
+        for (uint32_t k = (Bt + 63) >> 6; k < ((Bn + 63) >> 6); k++) ft[k] = t;
+        Bt = Bn;
+        t++;
+        p += (uint32_t)ch.y;
+    }
+}
+
+// ORs the bits of a field into word `w`.  The field covers global bits
+// [s, s+nb) with its least significant bit last; the word covers [w0, w0+64).
+__device__ __forceinline__ void place_field(uint64_t &w, int64_t w0, int64_t s, int nb, uint64_t val)
+{
+    int64_t rel = s + nb - 1 - w0;  // index of the field's last bit inside the word
+    if (rel < 0) return;
+    int64_t pos = 63 - rel;
+    if (pos >= 0) {
+        w |= val << pos;
+    } else if (-pos < nb) {
+        w |= val >> (-pos);
+    }
+}
+
+// One thread per 64-bit word of every SALZ block.
+__global__ void __launch_bounds__(256) k_emit_words(
+    const uint32_t *__restrict__ blkN, const int2 *__restrict__ choice, const uint32_t *__restrict__ blkTokens,
+    const uint32_t *__restrict__ blkBits, const uint32_t *__restrict__ blkSalzLen,
+    const uint64_t *__restrict__ blkOutOff, int framing, int logS, const uint32_t *__restrict__ tokPos,
+    const uint32_t *__restrict__ tokBit, const uint32_t *__restrict__ firstTok, uint8_t *__restrict__ out)
+{
+    const uint32_t wi = blockIdx.x * blockDim.x + threadIdx.x;   // b * (S/4) + k
+    const uint32_t b = wi >> (logS - 2);
+    const uint32_t k = wi & ((1u << (logS - 2)) - 1);
+    const uint32_t N = blkN[b];
+    if (blkSalzLen[b] > N + 4) return;
+    const uint32_t Bm = blkBits[b];
+    if (k >= ((Bm + 63) >> 6)) return;
+    const uint32_t m = blkTokens[b];
+    const size_t gb = (size_t)b << logS;
+    const uint32_t *tp = tokPos + gb, *tbit = tokBit + gb;
+    const int64_t w0 = (int64_t)k << 6;
+    const uint32_t t0 = firstTok[(gb >> 2) + k];
+    uint64_t w = 0;
+    uint32_t y = t0;
+    for (uint32_t t = t0; t < m; t++) {
+        const uint32_t Bt = tbit[t];
+        if ((int64_t)Bt >= w0 + 64) break;
+        int2 ch = choice[gb + tp[t]];
+        if (ch.y == 1) continue;  // literal: a single '0' bit
+        const uint32_t offs = (uint32_t)ch.x, len = (uint32_t)ch.y;
+        // pre-bits: '1' then the vnibbles of (offs-1)>>8, first-written nibble on top
+        int32_t v = (int32_t)((offs - 1u) >> 8);
+        uint64_t pv = (uint64_t)((v & 7) | 8);
+        int nn = 1;
+        v = (v >> 3) - 1;
+        while (v >= 0) {
+            pv |= (uint64_t)(v & 7) << (4 * nn);
+            nn++;
+            v = (v >> 3) - 1;
+        }
+        const int pre = 1 + 4 * nn;
+        pv |= 1ull << (4 * nn);
+        place_field(w, w0, (int64_t)Bt, pre, pv);
+        if (t == t0 && w0 >= (int64_t)Bt + pre) y = t0 + 1;
+        // post-bits: q zeros, '1', three low bits of len-3
+        const uint32_t q = (len - 3u) >> 3;
+        place_field(w, w0, (int64_t)Bt + pre + q, 4, 8u | ((len - 3u) & 7u));
+    }
+    uint8_t *dst = out + blkOutOff[b] + (framing ? 4 : 0) + 4 + 8 * (size_t)k + y;
+#pragma unroll
+    for (int i = 0; i < 8; i++) dst[i] = (uint8_t)(w >> (8 * i));
+}
+
+// Block header, optional u32 framing, and the PLAIN copy.
+// grid = (S / 4096, B), 256 threads.
+__global__ void __launch_bounds__(256) k_finalize(const uint8_t *__restrict__ T, size_t Tstride,
+                                                  const uint32_t *__restrict__ blkN,
+                                                  const uint32_t *__restrict__ blkSalzLen,
+                                                  const uint32_t *__restrict__ blkOutLen,
+                                                  const uint64_t *__restrict__ blkOutOff, int framing,
+                                                  uint8_t *__restrict__ out)
+{
+    const uint32_t b = blockIdx.y;
+    const uint32_t N = blkN[b];
+    const uint32_t salz = blkSalzLen[b];
+    const bool plain = salz > N + 4;
+    uint8_t *rec = out + blkOutOff[b];
+    if (blockIdx.x == 0 && threadIdx.x < 8) {
+        // ref lib/salz.c:755-772: type in the top byte, 24-bit length (overflow and all)
+        uint32_t hdr = plain ? (N & 0xffffffu) : ((1u << 24) | ((salz - 4) & 0xffffffu));
+        uint32_t fr = blkOutLen[b];
+        int i = threadIdx.x;
+        if (framing) {
+            rec[i] = (i < 4) ? (uint8_t)(fr >> (8 * i)) : (uint8_t)(hdr >> (8 * (i - 4)));
+        } else if (i < 4) {
+            rec[i] = (uint8_t)(hdr >> (8 * i));
+        }
+    }
+    if (plain) {
+        uint8_t *dst = rec + (framing ? 4 : 0) + 4;
+        const uint8_t *src = T + (size_t)b * Tstride;
+        uint32_t lo = blockIdx.x * 4096u;
+        for (uint32_t i = lo + threadIdx.x; i < min(N, lo + 4096u); i += 256) dst[i] = src[i];
+    }
+}
+
+}  // namespace
+
+int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st, LaunchCounter &lc)
+{
+    const size_t total = (size_t)bd.B * bd.S;
+    const uint32_t totalChunks = (uint32_t)(total >> PARSE_CHUNK_LOG);
+    const uint32_t chunksPerBlock = bd.S >> PARSE_CHUNK_LOG;
+    cudaMemsetAsync(ws.chunkEntry, 0xff, (size_t)totalChunks * 4, st);
+    k_chunk_entries<<<(bd.B + 31) / 32, 32, 0, st>>>(ws.blkN, ws.jump, bd.logS, bd.B, ws.chunkEntry);
+    k_walk_count<<<(totalChunks + 127) / 128, 128, 0, st>>>(ws.blkN, ws.choice, ws.chunkEntry, bd.logS,
+                                                            totalChunks, ws.chunkTok, ws.chunkBits);
+    k_block_scan<<<bd.B, 256, 0, st>>>(ws.blkN, chunksPerBlock, ws.chunkTok, ws.chunkBits, ws.blkTokens,
+                                       ws.blkBits, ws.blkSalzLen, ws.blkOutLen);
+    k_out_offsets<<<1, 32, 0, st>>>(ws.blkOutLen, bd.B, framing, ws.blkOutOff);
+    k_emit_tokens<<<(totalChunks + 127) / 128, 128, 0, st>>>(
+        ws.T, bd.Tstride, ws.blkN, ws.choice, ws.chunkEntry, ws.chunkTok, ws.chunkBits, ws.blkSalzLen,
+        ws.blkOutOff, framing, bd.logS, totalChunks, ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
+    k_emit_words<<<(uint32_t)((total >> 2) / 256), 256, 0, st>>>(ws.blkN, ws.choice, ws.blkTokens, ws.blkBits,
+                                                                 ws.blkSalzLen, ws.blkOutOff, framing, bd.logS,
+                                                                 ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
+    dim3 fg(bd.S / 4096, bd.B);
+    k_finalize<<<fg, 256, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.blkSalzLen, ws.blkOutLen, ws.blkOutOff, framing,
+                                   ws.out);
+    lc.launches += 7;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "salz_cuda: emit_build: %s\n", cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}

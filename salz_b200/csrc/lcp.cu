@@ -1,0 +1,263 @@
+// lcp.cu - PLCP by the phi method restricted to irreducible positions, LCP in
+// suffix-array order, and the min-pyramids the ANSV/range-min stage walks.
+//
+// salz itself never materialises an LCP array (it compares text directly,
+// ref lib/salz.c:492-538); this stage exists because the B200 design obtains
+// the match lengths as range minima of LCP.  Oracle: libsais_plcp/libsais_lcp
+// (ref 3rdparty/libsais/src/libsais.h:319,329).
+//
+//   Phi[i]  = SA[ISA[i]-1]           (none for the smallest suffix)
+//   i is irreducible  <=>  i == 0 or Phi[i] == 0 or T[i-1] != T[Phi[i]-1]
+//   irreducible: PLCP[i] by direct comparison (sum over a block is O(n log n))
+//   reducible:   PLCP[i] = PLCP[i-1] - 1
+// PLCP[i] + i is non-decreasing in i, so the fill is an inclusive max-scan of
+// V[i] = (irreducible ? PLCP[i] + i : 0) followed by "- i".
+#include "salz_dev.cuh"
+
+namespace {
+
+constexpr int LT = 1024;  // threads = positions per tile
+
+// Length of the common prefix of T[a..) and T[b..) limited to `cap` bytes,
+// thread-private part: at most `budget` bytes are examined; returns the
+// number of matching bytes found so far (== budget means "still equal").
+__device__ __forceinline__ uint32_t lcp_private(const uint8_t *Ta, const uint8_t *Tb, uint32_t cap, uint32_t budget)
+{
+    uint32_t l = 0;
+    uint32_t lim = min(cap, budget);
+    while (l < lim) {
+        uint64_t x = load_u64_unaligned(Ta + l) ^ load_u64_unaligned(Tb + l);
+        if (x) {
+            l += (uint32_t)(__ffsll((long long)x) - 1) >> 3;
+            return min(l, lim);
+        }
+        l += 8;
+    }
+    return lim;
+}
+
+__global__ void __launch_bounds__(LT) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
+                                                         const uint32_t *__restrict__ blkN,
+                                                         const uint32_t *__restrict__ rank,
+                                                         const uint32_t *__restrict__ SA, int logS,
+                                                         int32_t *__restrict__ V, int32_t *__restrict__ tileMax)
+{
+    __shared__ int32_t wmax[LT / 32];
+    const uint32_t Smask = (1u << logS) - 1;
+    const uint32_t g = blockIdx.x * LT + threadIdx.x;
+    const uint32_t b = g >> logS, p = g & Smask;
+    const uint32_t n = blkN[b] - 8;  // blkN >= 9 for every block of a batch
+    const uint8_t *Tb = T + (size_t)b * Tstride;
+    const int lane = threadIdx.x & 31;
+
+    int32_t v = 0;
+    uint32_t q = 0, cap = 0, l = 0;
+    bool pending = false;
+    if (p < n) {
+        uint32_t r = rank[g];
+        if ((r & Smask) == 0) {
+            v = (int32_t)p;  // smallest suffix of the block: PLCP = 0
+        } else {
+            q = SA[r - 1];
+            bool irreducible = (p == 0) || (q == 0) || (Tb[p - 1] != Tb[q - 1]);
+            if (irreducible) {
+                cap = n - max(p, q);
+                l = lcp_private(Tb + p, Tb + q, cap, 32);
+                pending = (l == 32 && cap > 32);
+                v = (int32_t)(l + p);
+            }
+        }
+    }
+    // Long matches: the whole warp compares 32 x 16 bytes per step.
+    unsigned todo = __ballot_sync(0xffffffffu, pending);
+    while (todo) {
+        int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        uint32_t p0 = __shfl_sync(0xffffffffu, p, src);
+        uint32_t q0 = __shfl_sync(0xffffffffu, q, src);
+        uint32_t cap0 = __shfl_sync(0xffffffffu, cap, src);
+        uint32_t l0 = 32;
+        for (;;) {
+            uint32_t off = l0 + lane * 16;
+            uint32_t mine = 16;  // matching bytes in my 16-byte window
+            if (off < cap0) {
+                uint64_t x = load_u64_unaligned(Tb + p0 + off) ^ load_u64_unaligned(Tb + q0 + off);
+                if (x) {
+                    mine = (uint32_t)(__ffsll((long long)x) - 1) >> 3;
+                } else {
+                    uint64_t y = load_u64_unaligned(Tb + p0 + off + 8) ^ load_u64_unaligned(Tb + q0 + off + 8);
+                    if (y) mine = 8 + ((uint32_t)(__ffsll((long long)y) - 1) >> 3);
+                }
+                mine = min(mine, cap0 - off);
+            } else {
+                mine = 0;
+            }
+            unsigned stop = __ballot_sync(0xffffffffu, mine < 16);
+            if (stop) {
+                int first = __ffs(stop) - 1;
+                uint32_t m = __shfl_sync(0xffffffffu, mine, first);
+                l0 = l0 + first * 16 + m;
+                break;
+            }
+            l0 += 512;
+        }
+        l0 = min(l0, cap0);
+        if (lane == src) v = (int32_t)(l0 + p);
+    }
+    V[g] = v;
+    // tile maximum
+    int32_t mx = v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) wmax[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int32_t w = wmax[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w = max(w, __shfl_xor_sync(0xffffffffu, w, o));
+        if (threadIdx.x == 0) tileMax[blockIdx.x] = w;
+    }
+}
+
+// One CTA per block: exclusive max-scan of the tile maxima, in place.
+__global__ void __launch_bounds__(256) k_plcp_scan_tiles(int32_t *__restrict__ tileMax, uint32_t tilesPerBlock)
+{
+    __shared__ int32_t part[256];
+    int32_t *tm = tileMax + (size_t)blockIdx.x * tilesPerBlock;
+    uint32_t per = (tilesPerBlock + 255) / 256;
+    uint32_t lo = threadIdx.x * per, hi = min(tilesPerBlock, lo + per);
+    int32_t s = 0;
+    for (uint32_t t = lo; t < hi; t++) s = max(s, tm[t]);
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int32_t run = 0;
+        for (int i = 0; i < 256; i++) {
+            int32_t c = part[i];
+            part[i] = run;
+            run = max(run, c);
+        }
+    }
+    __syncthreads();
+    s = part[threadIdx.x];
+    for (uint32_t t = lo; t < hi; t++) {
+        int32_t c = tm[t];
+        tm[t] = s;
+        s = max(s, c);
+    }
+}
+
+// PLCP[g] = inclusive-max(V)[g] - p, also scattered to LCP[ISA[g]].
+__global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ blkN,
+                                                   const uint32_t *__restrict__ rank, int logS,
+                                                   const int32_t *__restrict__ tileMax, int32_t *__restrict__ V,
+                                                   int32_t *__restrict__ lcp)
+{
+    __shared__ int32_t wmax[LT / 32];
+    const uint32_t Smask = (1u << logS) - 1;
+    const uint32_t g = blockIdx.x * LT + threadIdx.x;
+    const uint32_t b = g >> logS, p = g & Smask;
+    const uint32_t n = blkN[b] - 8;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int32_t v = (p < n) ? V[g] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int32_t t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v = max(v, t);
+    }
+    if (lane == 31) wmax[warp] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int32_t w = wmax[threadIdx.x];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int32_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w = max(w, t);
+        }
+        wmax[threadIdx.x] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    int32_t carry = tileMax[blockIdx.x];
+    if (warp > 0) carry = max(carry, wmax[warp - 1]);
+    v = max(v, carry);
+    if (p < n) {
+        int32_t pl = v - (int32_t)p;
+        V[g] = pl;
+        lcp[rank[g]] = pl;
+    }
+}
+
+// level-1 pyramid: minima over groups of 32 consecutive SA slots.
+__global__ void __launch_bounds__(256) k_pyramid_l1(const uint32_t *__restrict__ blkN,
+                                                    const uint32_t *__restrict__ SA,
+                                                    const int32_t *__restrict__ lcp, int logS,
+                                                    int32_t *__restrict__ outSA, int32_t *__restrict__ outLCP)
+{
+    const uint32_t Smask = (1u << logS) - 1;
+    const uint32_t s = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t b = s >> logS, r = s & Smask;
+    const uint32_t n = blkN[b] - 8;
+    int32_t a = (r < n) ? (int32_t)SA[s] : 0x7fffffff;
+    int32_t l = (r < n) ? lcp[s] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a = min(a, __shfl_xor_sync(0xffffffffu, a, o));
+        l = min(l, __shfl_xor_sync(0xffffffffu, l, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        outSA[s >> 5] = a;
+        outLCP[s >> 5] = l;
+    }
+}
+
+// level l+1 from level l (count = entries of the coarser level, all blocks).
+__global__ void __launch_bounds__(256) k_pyramid_up(const int32_t *__restrict__ inSA,
+                                                    const int32_t *__restrict__ inLCP, uint32_t outCount,
+                                                    int32_t *__restrict__ outSA, int32_t *__restrict__ outLCP)
+{
+    const uint32_t s = blockIdx.x * 256 + threadIdx.x;  // index into the finer level
+    const bool ok = (s >> 5) < outCount;
+    int32_t a = ok ? inSA[s] : 0x7fffffff;
+    int32_t l = ok ? inLCP[s] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a = min(a, __shfl_xor_sync(0xffffffffu, a, o));
+        l = min(l, __shfl_xor_sync(0xffffffffu, l, o));
+    }
+    if (ok && (threadIdx.x & 31) == 0) {
+        outSA[s >> 5] = a;
+        outLCP[s >> 5] = l;
+    }
+}
+
+}  // namespace
+
+int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
+{
+    const size_t total = (size_t)bd.B * bd.S;  // padded index space of this batch
+    const uint32_t tiles = (uint32_t)(total / LT);
+    const uint32_t tilesPerBlock = bd.S / LT;
+    k_plcp_irreducible<<<tiles, LT, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.rank, ws.SA, bd.logS, ws.plcp,
+                                             ws.tileMax);
+    k_plcp_scan_tiles<<<bd.B, 256, 0, st>>>(ws.tileMax, tilesPerBlock);
+    k_plcp_apply<<<tiles, LT, 0, st>>>(ws.blkN, ws.rank, bd.logS, ws.tileMax, ws.plcp, ws.lcp);
+    k_pyramid_l1<<<(uint32_t)(total / 256), 256, 0, st>>>(ws.blkN, ws.SA, ws.lcp, bd.logS, ws.pyrSA[1],
+                                                          ws.pyrLCP[1]);
+    lc.launches += 4;
+    // coarser levels: level l has (S >> 5l) entries per block; stop once <= 32
+    int l = 1;
+    while ((bd.S >> (5 * l)) > 32) {
+        size_t fine = (size_t)bd.B * (bd.S >> (5 * l));
+        uint32_t outCount = (uint32_t)(fine >> 5);
+        k_pyramid_up<<<(uint32_t)((fine + 255) / 256), 256, 0, st>>>(ws.pyrSA[l], ws.pyrLCP[l], outCount,
+                                                                     ws.pyrSA[l + 1], ws.pyrLCP[l + 1]);
+        lc.launches += 1;
+        l++;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "salz_cuda: lcp_build: %s\n", cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}

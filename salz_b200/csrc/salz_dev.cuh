@@ -1,0 +1,145 @@
+// salz_dev.cuh - internal device-side declarations shared by the .cu files.
+//
+// Index spaces used throughout (see DESIGN.md "Data layout in HBM"):
+//   b      block index inside the current batch, 0 <= b < B
+//   p      text position inside a block, 0 <= p < N_b   (n_b = N_b - 8 parsed)
+//   g      padded global index  g = b*S + p, S = power of two >= max block len
+//   slot   padded global suffix-array index b*S + r, r = rank inside block
+//   e,k    dense indices into the (compacted) sort list
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#define SALZ_INF 0x3fffffff
+
+struct BatchDesc {
+    int B;             // blocks in this batch
+    int logS;          // log2(S)
+    uint32_t S;        // index stride per block (power of two)
+    size_t Tstride;    // byte stride between blocks in d_T
+    uint32_t M;        // sum of n_b
+    uint32_t maxN;     // largest N_b
+};
+
+struct Workspace {
+    // capacity
+    size_t Bmax;
+    uint32_t S;
+    int logS;
+    size_t Mcap;       // Bmax * S
+
+    uint8_t *T;        // text, Bmax*Tstride + pad
+    size_t Tcap;
+    uint32_t *blkN;    // [Bmax]   N_b
+    uint32_t *elemStart; // [Bmax+1] prefix of n_b
+
+    // suffix sorting
+    uint64_t *keys[2];
+    uint32_t *vals[2];
+    uint32_t *slot[2];
+    uint32_t *prim;
+    uint32_t *rank;    // [Mcap] by g: padded global slot of the group head / final ISA
+    uint32_t *SA;      // [Mcap] by slot: local text position p
+    uint32_t *hist;    // [8][256] digit histograms for the coming sort
+    uint32_t *digitBase; // [8][256] exclusive scans of hist
+    uint32_t *tileState; // look-back state [tiles][256]
+    size_t tileStateCap; // in tiles
+    uint32_t *tileCounter; // [8] dynamic tile ids per pass
+    uint32_t *tileHist;  // fallback: [tiles][256]
+    // rerank scans
+    uint32_t *aggKeep;  // [rtiles]
+    uint32_t *aggHead;  // [rtiles]
+    uint32_t *counters; // [16] device scalars: [0]=kept count
+    uint32_t *h_counters; // pinned mirror
+
+    // LCP
+    int32_t *plcp;     // [Mcap] by g (first V = PLCP+i for irreducible, then PLCP)
+    int32_t *lcp;      // [Mcap] by slot
+    int32_t *tileMax;  // [Mcap/1024]
+    // min pyramids, levels 1.. (level l has Mcap >> (5l) entries)
+    int32_t *pyrSA[6];
+    int32_t *pyrLCP[6];
+    int nlevels;       // number of levels including level 0
+
+    // candidates / parse
+    int4 *cand;        // [Mcap] by g
+    int32_t *cost;     // [Mcap + Bmax... ] by g, n_b entry = 0  (size Mcap + 64)
+    int2 *choice;      // [Mcap] by g: (offs, len)
+    uint32_t *jump;    // [Mcap] by g: first position >= chunk end reached from p
+    // emit
+    uint32_t *chunkEntry; // [Mcap / CHUNK]
+    uint32_t *chunkTok;   // [Mcap / CHUNK] tokens starting in chunk -> exclusive prefix
+    uint32_t *chunkBits;  // [Mcap / CHUNK] bits of those tokens -> exclusive prefix
+    uint32_t *tokPos;     // [Mcap] by b*S + t
+    uint32_t *tokBit;     // [Mcap] by b*S + t : B_t
+    uint32_t *firstTok;   // [Mcap/4] by b*(S/4) + k
+    uint32_t *blkTokens;  // [Bmax] m
+    uint32_t *blkBits;    // [Bmax] B_m
+    uint32_t *blkSalzLen; // [Bmax] 4 + m + 8*ceil(B_m/64)
+    uint32_t *blkOutLen;  // [Bmax] final encoded length
+    uint64_t *blkOutOff;  // [Bmax+1] offset of block b's record in the packed stream
+    uint8_t *out;         // packed output stream
+    size_t outCap;
+};
+
+#define PARSE_CHUNK 2048      // positions per token-walk chunk
+#define PARSE_CHUNK_LOG 11
+
+// ---- small device helpers -------------------------------------------------
+
+// 8 bytes starting at an arbitrary byte address (little-endian), built from two
+// aligned 8-byte loads.  The text buffer is padded so addr+15 is readable.
+__device__ __forceinline__ uint64_t load_u64_unaligned(const uint8_t *addr)
+{
+    uintptr_t a = (uintptr_t)addr;
+    const uint64_t *w = (const uint64_t *)(a & ~(uintptr_t)7);
+    unsigned sh = (unsigned)(a & 7) * 8;
+    uint64_t lo = __ldg(w);
+    if (sh == 0)
+        return lo;
+    uint64_t hi = __ldg(w + 1);
+    return (lo >> sh) | (hi << (64 - sh));
+}
+
+// Bit cost of a factor (ref lib/salz.c:562-608): token bit + 8 direct offset
+// bits + 4 bits per vnibble of (offs-1)>>8 + GR3 code of len-3.
+__device__ __forceinline__ int vnibble_count(uint32_t v)
+{
+    int k = 1;
+    if (v >= 8) k = 2;
+    if (v >= 72) k = 3;
+    if (v >= 584) k = 4;
+    if (v >= 4680) k = 5;
+    if (v >= 37448) k = 6;
+    if (v >= 299592) k = 7;
+    if (v >= 2396744) k = 8;
+    return k;
+}
+__device__ __forceinline__ int factor_pre_bits(uint32_t offs)
+{
+    return 1 + 4 * vnibble_count((offs - 1u) >> 8);
+}
+__device__ __forceinline__ int factor_post_bits(uint32_t len)
+{
+    return (int)((len - 3u) >> 3) + 4;
+}
+__device__ __forceinline__ int factor_cost_bits(uint32_t offs, uint32_t len)
+{
+    return factor_pre_bits(offs) + 8 + factor_post_bits(len);
+}
+
+// ---- host-side launchers (one per pipeline stage) --------------------------
+struct LaunchCounter { uint64_t launches, sort_launches, sort_elems; };
+
+// sa.cu
+int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st,
+             LaunchCounter &lc, uint64_t &algBytes, int &rounds, float *msSort);
+// lcp.cu
+int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
+// parse.cu
+int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
+int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
+// emit.cu
+int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,
+               LaunchCounter &lc);
