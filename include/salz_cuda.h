@@ -119,6 +119,11 @@ int salz_cuda_suffix_arrays(salz_cuda_ctx *ctx, const uint8_t *texts,
                             const uint32_t *lens, size_t stride, size_t ntexts,
                             int32_t *sa_out);
 
+/* Page-locked host buffers for callers that stream large inputs (the CLI):
+ * copies from/to them run at full PCIe speed.  NULL on failure. */
+void *salz_cuda_host_alloc(size_t bytes);
+void salz_cuda_host_free(void *p);
+
 int salz_cuda_get_stats(const salz_cuda_ctx *ctx, salz_cuda_stats *out);
 void salz_cuda_reset_stats(salz_cuda_ctx *ctx);
 

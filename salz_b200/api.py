@@ -18,7 +18,7 @@ EXPORTS = [
     "salz_cuda_device_count", "salz_cuda_ctx_create", "salz_cuda_ctx_destroy", "salz_cuda_last_error",
     "salz_cuda_encode_blocks", "salz_cuda_encode_stream", "salz_cuda_encode_stream_device",
     "salz_cuda_debug_stages", "salz_cuda_suffix_arrays", "salz_cuda_get_stats", "salz_cuda_reset_stats",
-    "salz_cuda_set_sort_mode",
+    "salz_cuda_set_sort_mode", "salz_cuda_host_alloc", "salz_cuda_host_free",
 ]
 
 

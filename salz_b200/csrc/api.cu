@@ -160,6 +160,14 @@ extern "C" void salz_cuda_ctx_destroy(salz_cuda_ctx *c)
     delete c;
 }
 
+extern "C" void *salz_cuda_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void salz_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
+
 extern "C" const char *salz_cuda_last_error(const salz_cuda_ctx *c) { return c ? c->err : "no context"; }
 extern "C" void salz_cuda_set_sort_mode(salz_cuda_ctx *c, int mode) { if (c) c->sortMode = mode ? 1 : 0; }
 extern "C" int salz_cuda_get_stats(const salz_cuda_ctx *c, salz_cuda_stats *out)
@@ -262,6 +270,17 @@ static int stream_common(salz_cuda_ctx *c, const uint8_t *src, bool srcOnDevice,
         float ms;
         CKC(c, cudaEventElapsedTime(&ms, c->ev[6], c->ev[7]));
         c->stats.ms_h2d += ms;
+        // The reference writes the SALZ form into a buffer of
+        // salz_encoded_len_max(N) bytes before deciding on PLAIN; a nearly
+        // incompressible block can overflow it by < 8 bytes and the reference
+        // CLI then fails the whole file (ref lib/salz.c:260,274).  Same here.
+        for (int b = 0; b < B; b++) {
+            size_t N = c->h_blkN[b];
+            if (c->h_salzLen[b] > 4 + N + (N + 63) / 64 * 8) {
+                set_err(c, "block %zu: intermediate stream exceeds salz_encoded_len_max (reference fails too)", b0 + b);
+                return -1;
+            }
+        }
         const size_t produced = (size_t)c->h_outOff[B];
         if (outPos + produced > dst_cap) { set_err(c, "output buffer too small"); return -1; }
         CKC(c, cudaEventRecord(c->ev[6], st));
