@@ -131,6 +131,11 @@ void salz_cuda_reset_stats(salz_cuda_ctx *ctx);
  * decoupled look-back scatter (default). */
 void salz_cuda_set_sort_mode(salz_cuda_ctx *ctx, int mode);
 
+/* Run this context's copies and kernels on the caller's CUDA stream
+ * (a cudaStream_t passed as void *; NULL restores the context's own stream),
+ * so that events the caller records on that stream bracket the work. */
+void salz_cuda_set_stream(salz_cuda_ctx *ctx, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

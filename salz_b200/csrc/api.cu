@@ -13,6 +13,7 @@
 struct salz_cuda_ctx {
     int device;
     cudaStream_t stream;
+    cudaStream_t ownStream;
     Workspace ws;
     size_t maxBlockLen;
     int sortMode;
@@ -99,7 +100,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
         return nullptr;
     }
     const size_t M = ws.Mcap, B = ws.Bmax;
-    bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    bool ok = cudaStreamCreateWithFlags(&c->ownStream, cudaStreamNonBlocking) == cudaSuccess;
+    c->stream = c->ownStream;
     for (int i = 0; i < 8 && ok; i++) ok = cudaEventCreate(&c->ev[i]) == cudaSuccess;
     ws.Tcap = M + 256;
     ok = ok && dalloc(c, &ws.T, ws.Tcap);
@@ -156,7 +158,7 @@ extern "C" void salz_cuda_ctx_destroy(salz_cuda_ctx *c)
     if (c->h_outOff) cudaFreeHost(c->h_outOff);
     for (int i = 0; i < 8; i++)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->ownStream) cudaStreamDestroy(c->ownStream);
     delete c;
 }
 
@@ -170,6 +172,12 @@ extern "C" void salz_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 extern "C" const char *salz_cuda_last_error(const salz_cuda_ctx *c) { return c ? c->err : "no context"; }
 extern "C" void salz_cuda_set_sort_mode(salz_cuda_ctx *c, int mode) { if (c) c->sortMode = mode ? 1 : 0; }
+extern "C" void salz_cuda_set_stream(salz_cuda_ctx *c, void *stream)
+{
+    if (!c) return;
+    cudaStreamSynchronize(c->stream);
+    c->stream = stream ? (cudaStream_t)stream : c->ownStream;
+}
 extern "C" int salz_cuda_get_stats(const salz_cuda_ctx *c, salz_cuda_stats *out)
 {
     if (!c || !out) return -1;

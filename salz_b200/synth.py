@@ -41,18 +41,34 @@ def english_like(size, seed=1, vocab=4096, zipf_s=1.3):
     idx = rng.choice(vocab, size=nw, p=pw)
     seps = rng.choice(np.array([0, 0, 0, 0, 0, 0, 0, 1, 2, 3]), size=nw)
     septab = [b" ", b", ", b". ", b"\n"]
-    parts = []
-    total = 0
-    for w, s in zip(idx, seps):
-        t = words[w] + septab[s]
-        parts.append(t)
-        total += len(t)
-        if total >= size:
-            break
-    buf = b"".join(parts)
-    while len(buf) < size:
-        buf += buf[: size - len(buf)]
-    return np.frombuffer(buf[:size], dtype=np.uint8).copy()
+    # token table: row = word * 4 + separator, padded to 16 bytes
+    tab = np.zeros((vocab * 4, 16), np.uint8)
+    tlen = np.zeros(vocab * 4, np.int64)
+    for w in range(vocab):
+        for s in range(4):
+            t = words[w] + septab[s]
+            tab[w * 4 + s, : len(t)] = np.frombuffer(t, np.uint8)
+            tlen[w * 4 + s] = len(t)
+    tok = idx.astype(np.int64) * 4 + seps
+    lens = tlen[tok]
+    ends = np.cumsum(lens)
+    k = min(int(np.searchsorted(ends, size, side="left")) + 1, nw)  # tokens until >= size bytes
+    total = int(ends[k - 1])
+    out = np.empty(max(total, size), dtype=np.uint8)
+    step = 1 << 21
+    for lo in range(0, k, step):
+        hi = min(k, lo + step)
+        ln = lens[lo:hi]
+        first = int(ends[lo] - lens[lo])
+        nbytes = int(ends[hi - 1]) - first
+        tokid = np.repeat(np.arange(lo, hi), ln)
+        within = np.arange(nbytes) - np.repeat(ends[lo:hi] - ln - first, ln)
+        out[first: first + nbytes] = tab[tok[tokid], within]
+    while total < size:
+        ln = min(total, size - total)
+        out[total: total + ln] = out[:ln]
+        total += ln
+    return out[:size].copy()
 
 
 def dna_like(size, seed=2, block=1 << 20, repeats_per_block=3, kmin=6, kmax=19):

@@ -1,0 +1,247 @@
+"""GPU tier (run on the B200 box: pytest -m gpu): the CUDA path, called through
+the C ABI (include/salz_cuda.h via ctypes) and through the host library /
+CLI, against the oracle.  Everything is integer/byte work: the bar is
+bit-exact equality, stage by stage and on the final bytes."""
+import ctypes as C
+import hashlib
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import salz_b200
+from salz_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))
+
+
+@pytest.fixture(scope="module")
+def orc(port):
+    """The compiled reference when its prebuilt .so travelled here, else the restatement."""
+    from oracle.binding import Ref
+    return Ref() if Ref.available() else port
+
+
+def _first_diff(a, b):
+    a = np.asarray(a); b = np.asarray(b)
+    if a.shape != b.shape:
+        return "shape %s vs %s" % (a.shape, b.shape)
+    d = np.nonzero(a != b)
+    if len(d[0]) == 0:
+        return None
+    i = tuple(x[0] for x in d)
+    return "first diff at %s: got %s want %s (%d differ)" % (i, a[i], b[i], len(d[0]))
+
+
+def _check_stages(enc, orc, name, data):
+    got, want = enc.stages(data), orc.stages(data)
+    n = len(data) - 8
+    for k in ("sa", "plcp", "lcp"):
+        assert _first_diff(got[k], want[k]) is None, (name, k, _first_diff(got[k], want[k]))
+    assert _first_diff(got["cand"][1:], want["cand"][1:]) is None, (name, "cand")
+    assert _first_diff(got["parse"][1:n], want["parse"][1:n]) is None, (name, "parse")
+    assert got["out"] == want["out"], (name, "bytes")
+
+
+def test_known_answers(enc):
+    # SURVEY.md Appendix A
+    assert enc.encode(b"abcdefghi").hex() == "09000000616263646566676869"
+    assert enc.encode(b"a" * 64).hex() == "120000010000000000000c6061006161616161616161"
+    assert enc.encode(b"abcabcabcabcabcabcabcabcXYZ01234").hex() == \
+        "1400000100000000000028186162630258595a3031323334"
+
+
+def test_golden_vectors(enc):
+    for vec in GOLDEN["vectors"]:
+        data = bytes.fromhex(vec["input"])
+        st = enc.stages(data)
+        assert st["out"].hex() == vec["output"], vec["name"]
+        if "sa" in vec:
+            assert st["sa"].tolist() == vec["sa"], vec["name"]
+            assert st["lcp"].tolist() == vec["lcp"], vec["name"]
+            assert st["cand"][1:].reshape(-1).tolist() == vec["cand"], vec["name"]
+            assert st["parse"][1:].reshape(-1).tolist() == vec["parse"], vec["name"]
+
+
+def test_golden_digests_1mib(enc):
+    gens = {"english_1MiB": lambda: synth.english_like(1 << 20, seed=5),
+            "dna_1MiB": lambda: synth.dna_like(1 << 20, seed=7),
+            "markov_300k": lambda: synth.markov_text(300000, seed=42)}
+    for d in GOLDEN["digests"]:
+        if d["name"] in gens:
+            out = enc.encode(gens[d["name"]]())
+            assert len(out) == d["len"] and hashlib.sha256(out).hexdigest() == d["sha256"], d["name"]
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_small_cases_all_stages(enc, orc, mode):
+    enc.set_sort_mode(mode)
+    try:
+        cases = synth.small_cases(3) + [
+            ("zeros", np.zeros(100, np.uint8)),
+            ("zero_tail", np.concatenate([np.arange(50, dtype=np.uint8) + 1, np.zeros(20, np.uint8)])),
+            ("n9", np.frombuffer(b"abcdefghi", np.uint8)),
+            ("n10", np.frombuffer(b"aaaaaaaaaa", np.uint8)),
+            ("n11", np.frombuffer(b"abababababa", np.uint8)),
+        ]
+        for name, data in cases:
+            _check_stages(enc, orc, name, data)
+    finally:
+        enc.set_sort_mode(1)
+
+
+def test_medium_cases_all_stages(enc, orc):
+    cases = [("eng64k", synth.english_like(65536 + 100, seed=9)),
+             ("dna200k", synth.dna_like(200000, seed=3, block=200000)),
+             ("a100k", np.full(100000, 97, np.uint8)),
+             ("rand50k", synth.uniform_random(50000, seed=1)),
+             ("ab_period", np.resize(np.frombuffer(b"ab", np.uint8), 70001)),
+             ("markov100k", synth.markov_text(100000, seed=42)),
+             ("eng1M", synth.english_like(1 << 20, seed=5)),
+             ("dna1M", synth.dna_like(1 << 20, seed=7)),
+             ("a1M", np.full(1 << 20, 0x61, np.uint8)),
+             ("rand1M", synth.uniform_random(1 << 20, seed=4))]
+    for name, data in cases:
+        _check_stages(enc, orc, name, data)
+
+
+def test_encode_blocks_error_semantics(enc, orc):
+    """salz_encode_safe conventions (ref lib/salz.c:777-823)."""
+    data = synth.english_like(5000, seed=3)
+    full = orc.encode(data)
+    blocks = [b"", b"x" * 7, b"x" * 8, data, b"x" * 9]
+    out = enc.encode_blocks(blocks)
+    assert out[0] is None and out[1] is None and out[2] is None
+    assert out[3] == full and out[4] == orc.encode(b"x" * 9)
+    for cap in (3, 4, len(full) - 1, len(full), len(full) + 1):
+        assert enc.encode(data, cap=cap) == orc.encode(data, cap=cap), cap
+    rnd = synth.uniform_random(5000, seed=3)
+    for cap in (5004, 5003, 5004 + 8 * 79 - 1, 5004 + 8 * 79):
+        assert enc.encode(rnd, cap=cap) == orc.encode(rnd, cap=cap), cap
+
+
+def test_batched_stream_matches_per_block_oracle(enc, orc):
+    """CLI block loop (ref programs/salzcli.c:143-179): framed records, ragged tail,
+    more blocks than one batch holds, PLAIN and SALZ blocks mixed."""
+    bl = 1 << 18
+    data = np.concatenate([synth.english_like(9 * bl, seed=11), synth.dna_like(4 * bl, seed=12, block=bl),
+                           synth.uniform_random(2 * bl, seed=13), np.full(3 * bl + 777, 98, np.uint8)])
+    stream, sizes = enc.encode_stream(data, bl)
+    want = b""
+    wsizes = []
+    for off in range(0, len(data), bl):
+        blk = orc.encode(data[off: off + bl])
+        wsizes.append(len(blk))
+        want += len(blk).to_bytes(4, "little") + blk
+    assert sizes.tolist() == wsizes
+    assert stream == want
+
+
+def test_stream_rejects_tiny_tail(enc):
+    bl = 1 << 15
+    with pytest.raises(salz_b200.SalzCudaError):
+        enc.encode_stream(np.zeros(bl + 8, np.uint8), bl)
+
+
+def test_suffix_arrays_entry(enc, orc):
+    texts = [synth.english_like(50000, seed=1), synth.dna_like(70001, seed=2, block=70001),
+             np.full(30000, 7, np.uint8), synth.uniform_random(9999, seed=5), np.frombuffer(b"banana", np.uint8)]
+    sas = enc.suffix_arrays(texts)
+    for t, sa in zip(texts, sas):
+        assert np.array_equal(sa, orc.suffix_array(t))
+
+
+def test_level9_block(orc):
+    """One 16 MiB block (CLI level 9): bytes identical, header quirk F4 on random data."""
+    e = salz_b200.SalzCuda(0, 1 << 24, 1)
+    try:
+        data = synth.english_like(1 << 24, seed=31)
+        assert e.encode(data) == orc.encode(data)
+        a = np.full(1 << 24, 0x61, np.uint8)
+        out = e.encode(a)
+        d = [x for x in GOLDEN["digests"] if x["name"] == "a_x_16MiB"][0]
+        assert len(out) == d["len"] == 262166 and hashlib.sha256(out).hexdigest() == d["sha256"]
+        r = synth.uniform_random(1 << 24, seed=4)
+        out = e.encode(r)
+        d = [x for x in GOLDEN["digests"] if x["name"] == "random_16MiB"][0]
+        assert out[:4].hex() == "00000000" == d["head"]
+        assert len(out) == d["len"] and hashlib.sha256(out).hexdigest() == d["sha256"]
+    finally:
+        e.close()
+
+
+def _host_lib():
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "lib")], check=True)
+    lib = C.CDLL(os.path.join(ROOT, "lib", "libsalz.so"))
+    lib.salz_encode_safe.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.POINTER(C.c_size_t)]
+    lib.salz_decode_safe.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.POINTER(C.c_size_t)]
+    return lib
+
+
+def test_host_library_encode_roundtrip(orc):
+    """lib/salz.h entry points: salz_encode_safe runs the CUDA path, salz_decode_safe restores."""
+    lib = _host_lib()
+    for data in (synth.english_like(300000, seed=1).tobytes(), b"abcdefghi", bytes(5000)):
+        cap = salz_b200.encoded_len_max(len(data))
+        dst = C.create_string_buffer(cap)
+        n = C.c_size_t(cap)
+        assert lib.salz_encode_safe(data, len(data), dst, C.byref(n)) == 0
+        assert dst.raw[: n.value] == orc.encode(data)
+        back = C.create_string_buffer(len(data) + 8)
+        m = C.c_size_t(len(data))
+        assert lib.salz_decode_safe(dst.raw[: n.value], n.value, back, C.byref(m)) == 0
+        assert back.raw[: m.value] == data
+    n = C.c_size_t(100)
+    assert lib.salz_encode_safe(b"12345678", 8, C.create_string_buffer(100), C.byref(n)) == -1
+
+
+def test_full_size_roundtrip_properties(orc):
+    """Size-independent checks at a large size (64 MiB + 4096 English-like, level 5):
+    every block decodes back to its input, sizes sum up, sampled blocks equal the oracle."""
+    lib = _host_lib()
+    bl = 1 << 20
+    data = synth.english_like((64 << 20) + 4096, seed=1)
+    e = salz_b200.SalzCuda(0, bl, 65)
+    try:
+        stream, sizes = e.encode_stream(data, bl)
+    finally:
+        e.close()
+    assert len(stream) == int(sizes.astype(np.int64).sum()) + 4 * len(sizes)
+    pos = 0
+    back = C.create_string_buffer(bl + 8)
+    for b, sz in enumerate(sizes.tolist()):
+        assert int.from_bytes(stream[pos: pos + 4], "little") == sz
+        rec = stream[pos + 4: pos + 4 + sz]
+        blk = data[b * bl: (b + 1) * bl].tobytes()
+        m = C.c_size_t(len(blk))
+        assert lib.salz_decode_safe(rec, sz, back, C.byref(m)) == 0 and back.raw[: m.value] == blk, b
+        if b in (0, 17, 40, len(sizes) - 1):
+            assert rec == orc.encode(blk), b
+        pos += 4 + sz
+    assert pos == len(stream)
+
+
+def test_cli_compress_matches_reference_cli(tmp_path):
+    """`salz -k -5 file` writes the same bytes as the reference CLI and the reference decodes it."""
+    ref_cli = os.path.join(ROOT, "oracle", "_ref", "salz_ref")
+    if not os.path.exists(ref_cli):
+        pytest.skip("prebuilt reference CLI absent")
+    _host_lib()
+    data = np.concatenate([synth.english_like(5 << 20, seed=2), synth.uniform_random((1 << 20) + 4096, seed=3)])
+    a = tmp_path / "a.bin"; b = tmp_path / "b.bin"
+    a.write_bytes(data.tobytes()); b.write_bytes(data.tobytes())
+    env = dict(os.environ, SALZ_BATCH_MIB="4")
+    subprocess.run([os.path.join(ROOT, "programs", "salz"), "-k", "-q", "-5", str(a)], check=True, env=env)
+    subprocess.run([ref_cli, "-k", "-q", "-5", str(b)], check=True)
+    assert (tmp_path / "a.bin.salz").read_bytes() == (tmp_path / "b.bin.salz").read_bytes()
+    a.unlink()
+    subprocess.run([ref_cli, "-d", "-q", str(a) + ".salz"], check=True)
+    assert a.read_bytes() == data.tobytes()
+    # exact multiple of the block size fails like the reference
+    c = tmp_path / "c.bin"
+    c.write_bytes(bytes(1 << 15))
+    assert subprocess.run([os.path.join(ROOT, "programs", "salz"), "-k", "-q", "-0", str(c)]).returncode != 0
