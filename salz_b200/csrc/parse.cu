@@ -122,122 +122,190 @@ __global__ void __launch_bounds__(256) k_ansv(Pyr py, const uint32_t *__restrict
 }
 
 // ---------------------------------------------------------------------------
-// Optimal parse.  One warp per block walks 32-position windows right to left.
-// Inside a window, lane l owns position q - l (q = right end).  Costs of
-// targets beyond the window are already final and are gathered in parallel;
-// the literal chain inside the window is a prefix-min scan in (min,+); factor
-// edges that land inside the window are relaxed to a fixpoint (at most ~10
-// iterations because factors are >= 3 long).  Costs are exact, so the choice
-// can be recomputed per lane with the reference's comparison order.
+// Optimal parse.  One CTA per block: warp 0 is the consumer that walks the
+// serial cost chain in 32-position windows right to left, warps 1..3 are
+// producers that stage the next PC-position chunk (candidates, edge weights,
+// and the final costs of targets that lie at least one whole chunk to the
+// right) in shared memory while the consumer works, so the chain never waits
+// on global memory.
 //
-// Also produced: jump[p] = first position >= the end of p's PARSE_CHUNK that
-// the chosen parse reaches from p (used by the token walk in emit.cu).
+// Inside a window lane l owns position q - l (q = right end).  Targets
+//   - at least one chunk ahead of the consumer: weight + cost staged ("far"),
+//   - beyond the window but inside the last two chunks: cost ring in smem,
+//   - inside the window: relaxed to a fixpoint with shuffles (at most ~10
+//     iterations because factors are >= 3 long).
+// The literal chain inside the window is a prefix-min scan in (min,+).  Costs
+// are exact, so the choice is recomputed per lane with the reference's
+// comparison order (strict '<': literal, PSV, NSV; ref lib/salz.c:622-661).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(32) k_parse(const int4 *__restrict__ cand, const uint32_t *__restrict__ blkN,
-                                              int logS, int32_t *cost, int2 *__restrict__ choice,
-                                              uint32_t *__restrict__ jump)
+constexpr int PC = 512;            // positions per staged chunk
+constexpr int PARSE_THREADS = 128; // 1 consumer warp + 3 producer warps
+constexpr int NOT_FAR = -1;
+
+__device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const int32_t *cs, uint32_t n,
+                                            uint32_t chunk, int4 *sa, int4 *sb, int tid, int nthreads)
 {
-    __shared__ uint32_t ring[PARSE_CHUNK];
+    const uint32_t base = chunk * PC;
+    const uint32_t farFrom = (chunk + 2) * PC;  // targets >= this are final and visible
+    for (uint32_t i = tid; i < PC; i += nthreads) {
+        const uint32_t p = base + i;
+        int4 a = make_int4(0, 0, NOT_FAR, 0), b = make_int4(0, 0, NOT_FAR, 0);
+        if (p >= 1 && p < n) {
+            int4 c = cd[p];
+            if (c.y >= 3) {
+                a.x = c.y;
+                a.y = factor_cost_bits((uint32_t)c.x, (uint32_t)c.y);
+                a.w = c.x;
+                uint32_t t = p + (uint32_t)c.y;
+                if (t >= farFrom) a.z = a.y + __ldcg(&cs[t]);
+            }
+            if (c.w >= 3) {
+                b.x = c.w;
+                b.y = factor_cost_bits((uint32_t)c.z, (uint32_t)c.w);
+                b.w = c.z;
+                uint32_t t = p + (uint32_t)c.w;
+                if (t >= farFrom) b.z = b.y + __ldcg(&cs[t]);
+            }
+        }
+        sa[i] = a;
+        sb[i] = b;
+    }
+}
+
+__global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict__ cand,
+                                                         const uint32_t *__restrict__ blkN, int logS, int32_t *cost,
+                                                         int2 *__restrict__ choice)
+{
+    __shared__ int4 stA[2][PC], stB[2][PC];
+    __shared__ int32_t ring[2 * PC];
     const uint32_t b = blockIdx.x;
-    const int lane = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t N = blkN[b];
     const uint32_t n = N - 8;
     const size_t gb = (size_t)b << logS;
     const int4 *cd = cand + gb;
     int32_t *cs = cost + gb + b;  // n_b + 1 entries per block (stride S + 1)
     int2 *ch = choice + gb;
-    uint32_t *jp = jump + gb;
+
+    const uint32_t nChunks = (N + PC - 1) / PC;
+    stage_chunk(cd, cs, n, nChunks - 1, stA[(nChunks - 1) & 1], stB[(nChunks - 1) & 1], tid, PARSE_THREADS);
+    __syncthreads();
 
     int32_t costRight = SALZ_INF;  // cost[q+1] of the window being processed
-    const uint32_t lastWin = (N - 1) >> 5;
-    for (uint32_t w = lastWin + 1; w-- > 0;) {
-        const uint32_t q = (w << 5) + 31;
-        const uint32_t p = q - lane;
-        const uint32_t chunkEnd = ((p >> PARSE_CHUNK_LOG) + 1) << PARSE_CHUNK_LOG;  // same for all lanes
+    for (uint32_t c = nChunks; c-- > 0;) {
+        if (warp != 0) {
+            if (c > 0) stage_chunk(cd, cs, n, c - 1, stA[(c - 1) & 1], stB[(c - 1) & 1], tid - 32, PARSE_THREADS - 32);
+        } else {
+            const int4 *sa = stA[c & 1], *sb = stB[c & 1];
+            const uint32_t lastP = min(N - 1, c * PC + PC - 1);
+            for (uint32_t w = (lastP >> 5) + 1; w-- > (c * PC) >> 5;) {
+                const uint32_t q = (w << 5) + 31;
+                const uint32_t p = q - lane;
+                const int4 ra = sa[p & (PC - 1)], rb = sb[p & (PC - 1)];
+                const uint32_t l1 = (uint32_t)ra.x, l2 = (uint32_t)rb.x;
+                const int32_t a1 = ra.y, a2 = rb.y;
+                int32_t f1 = SALZ_INF, f2 = SALZ_INF;  // edge weight + final target cost
+                bool near1 = false, near2 = false;
+                if (l1 >= 3) {
+                    if (ra.z != NOT_FAR) f1 = ra.z;
+                    else if (l1 <= (uint32_t)lane) near1 = true;
+                    else f1 = a1 + ring[(p + l1) & (2 * PC - 1)];
+                }
+                if (l2 >= 3) {
+                    if (rb.z != NOT_FAR) f2 = rb.z;
+                    else if (l2 <= (uint32_t)lane) near2 = true;
+                    else f2 = a2 + ring[(p + l2) & (2 * PC - 1)];
+                }
+                int32_t x = (p == n) ? 0 : min(f1, f2);  // cost[n] = 0 (ref lib/salz.c:621)
+                const int32_t xfar = x;
 
-        // --- candidates and far costs ---
-        int32_t a1 = SALZ_INF, a2 = SALZ_INF;     // edge weights
-        uint32_t l1 = 0, l2 = 0, o1 = 0, o2 = 0;
-        int32_t f1 = SALZ_INF, f2 = SALZ_INF;     // edge weight + far target cost
-        bool near1 = false, near2 = false;
-        int32_t x;                                // best non-literal, non-near option so far
-        if (p >= 1 && p < n) {
-            int4 c = cd[p];
-            if (c.y >= 3) {
-                o1 = (uint32_t)c.x; l1 = (uint32_t)c.y;
-                a1 = factor_cost_bits(o1, l1);
-                if (l1 <= (uint32_t)lane) near1 = true;
-                else f1 = a1 + __ldcg(&cs[p + l1]);
-            }
-            if (c.w >= 3) {
-                o2 = (uint32_t)c.z; l2 = (uint32_t)c.w;
-                a2 = factor_cost_bits(o2, l2);
-                if (l2 <= (uint32_t)lane) near2 = true;
-                else f2 = a2 + __ldcg(&cs[p + l2]);
-            }
-        }
-        if (p == n) x = 0;                    // cost[n] = 0 (ref lib/salz.c:621)
-        else x = min(f1, f2);                 // INF for p > n and p == 0
-        const int32_t xfar = x;
-
-        // --- fixpoint over in-window edges ---
-        int32_t cst;
-        const unsigned anyNear = __ballot_sync(0xffffffffu, near1 || near2);
-        for (;;) {
-            // cost[l] = min( min_{k<=l} x[k] + 9(l-k), costRight + 9(l+1) )
-            int32_t y = x - 9 * lane;
+                // --- fixpoint over in-window edges ---
+                int32_t cst;
+                const unsigned anyNear = __ballot_sync(0xffffffffu, near1 || near2);
+                for (;;) {
+                    // cost[l] = min( min_{k<=l} x[k] + 9(l-k), costRight + 9(l+1) )
+                    int32_t y = x - 9 * lane;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                int32_t t = __shfl_up_sync(0xffffffffu, y, o);
-                if (lane >= o) y = min(y, t);
+                    for (int o = 1; o < 32; o <<= 1) {
+                        int32_t t = __shfl_up_sync(0xffffffffu, y, o);
+                        if (lane >= o) y = min(y, t);
+                    }
+                    cst = min(y + 9 * lane, costRight + 9 * (lane + 1));
+                    if (p > n) cst = SALZ_INF;
+                    if (!anyNear) break;
+                    int32_t t1 = __shfl_sync(0xffffffffu, cst, near1 ? (lane - (int)l1) : 0);
+                    int32_t t2 = __shfl_sync(0xffffffffu, cst, near2 ? (lane - (int)l2) : 0);
+                    int32_t nx = xfar;
+                    if (near1) nx = min(nx, a1 + t1);
+                    if (near2) nx = min(nx, a2 + t2);
+                    bool changed = nx < x;
+                    x = min(x, nx);
+                    if (!__any_sync(0xffffffffu, changed)) break;
+                }
+
+                // --- choice with the reference's tie-break ---
+                int32_t right = __shfl_up_sync(0xffffffffu, cst, 1);
+                if (lane == 0) right = costRight;
+                int32_t t1 = __shfl_sync(0xffffffffu, cst, near1 ? (lane - (int)l1) : 0);
+                int32_t t2 = __shfl_sync(0xffffffffu, cst, near2 ? (lane - (int)l2) : 0);
+                int32_t c1 = near1 ? a1 + t1 : f1;
+                int32_t c2 = near2 ? a2 + t2 : f2;
+                int32_t best = 9 + right;
+                uint32_t bo = 0, bl = 1;
+                if (l1 >= 3 && c1 < best) { best = c1; bo = (uint32_t)ra.w; bl = l1; }
+                if (l2 >= 3 && c2 < best) { best = c2; bo = (uint32_t)rb.w; bl = l2; }
+                if (p == 0 || p >= n) { bo = 0; bl = 1; }  // forced literals: position 0 and the 8-byte tail
+
+                ring[p & (2 * PC - 1)] = cst;
+                if (p < N) {
+                    if (p <= n) cs[p] = cst;
+                    ch[p] = make_int2((int)bo, (int)bl);
+                }
+                costRight = __shfl_sync(0xffffffffu, cst, 31);
+                __syncwarp();
             }
-            cst = min(y + 9 * lane, costRight + 9 * (lane + 1));
-            if (p > n) cst = SALZ_INF;
-            if (!anyNear) break;
-            int32_t t1 = __shfl_sync(0xffffffffu, cst, near1 ? (lane - (int)l1) : 0);
-            int32_t t2 = __shfl_sync(0xffffffffu, cst, near2 ? (lane - (int)l2) : 0);
-            int32_t nx = xfar;
-            if (near1) nx = min(nx, a1 + t1);
-            if (near2) nx = min(nx, a2 + t2);
-            bool changed = nx < x;
-            x = min(x, nx);
-            if (!__any_sync(0xffffffffu, changed)) break;
         }
+        __syncthreads();
+    }
+}
 
-        // --- choice with the reference's tie-break ---
-        int32_t right = __shfl_up_sync(0xffffffffu, cst, 1);
-        if (lane == 0) right = costRight;
-        int32_t t1 = __shfl_sync(0xffffffffu, cst, near1 ? (lane - (int)l1) : 0);
-        int32_t t2 = __shfl_sync(0xffffffffu, cst, near2 ? (lane - (int)l2) : 0);
-        int32_t c1 = near1 ? a1 + t1 : f1;
-        int32_t c2 = near2 ? a2 + t2 : f2;
-        int32_t best = 9 + right;
-        uint32_t bo = 0, bl = 1;
-        if (l1 >= 3 && c1 < best) { best = c1; bo = o1; bl = l1; }
-        if (l2 >= 3 && c2 < best) { best = c2; bo = o2; bl = l2; }
-        if (p == 0 || p >= n) { bo = 0; bl = 1; }  // forced literals: position 0 and the 8-byte tail
-
-        // --- chunk exit pointers ---
-        uint32_t t = p + bl;  // next token start
+// jump[p] = first position >= the end of p's PARSE_CHUNK that the chosen parse
+// reaches from p (pointer jumping inside the chunk; used by the token walk in
+// emit.cu).  One CTA per chunk.
+__global__ void __launch_bounds__(256) k_jump(const uint32_t *__restrict__ blkN, const int2 *__restrict__ choice,
+                                              int logS, uint32_t *__restrict__ jump)
+{
+    __shared__ uint32_t nxt[PARSE_CHUNK];
+    const uint32_t chunksPerBlock = 1u << (logS - PARSE_CHUNK_LOG);
+    const uint32_t b = blockIdx.x / chunksPerBlock, c = blockIdx.x % chunksPerBlock;
+    const uint32_t N = blkN[b];
+    const uint32_t base = c << PARSE_CHUNK_LOG;
+    if (base >= N) return;
+    const uint32_t end = min(N, base + PARSE_CHUNK);
+    const size_t gb = (size_t)b << logS;
+    constexpr int PER = PARSE_CHUNK / 256;
+    uint32_t v[PER];
 #pragma unroll
-        for (int s = 0; s < 5; s++) {
-            bool inwin = (t <= q) && (t < N);
-            uint32_t tt = __shfl_sync(0xffffffffu, t, inwin ? (int)(q - t) : 0);
-            if (inwin) t = tt;
-        }
-        uint32_t j = t;
-        if (t < chunkEnd && t < N) j = ring[t & (PARSE_CHUNK - 1)];
-        __syncwarp();
-        ring[p & (PARSE_CHUNK - 1)] = j;
-        __syncwarp();
-
-        if (p < N) {
-            if (p <= n) cs[p] = cst;
-            ch[p] = make_int2((int)bo, (int)bl);
-            jp[p] = j;
-        }
-        costRight = __shfl_sync(0xffffffffu, cst, 31);
-        __syncwarp();
+    for (int i = 0; i < PER; i++) {
+        uint32_t p = base + threadIdx.x + i * 256;
+        v[i] = (p < end) ? p + (uint32_t)choice[gb + p].y : end;
+        nxt[threadIdx.x + i * 256] = v[i];
+    }
+    __syncthreads();
+    for (int it = 0; it < PARSE_CHUNK_LOG; it++) {
+        bool moved = false;
+#pragma unroll
+        for (int i = 0; i < PER; i++)
+            if (v[i] < end) { v[i] = nxt[v[i] - base]; moved = true; }
+        if (!__syncthreads_or(moved)) break;
+#pragma unroll
+        for (int i = 0; i < PER; i++) nxt[threadIdx.x + i * 256] = v[i];
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < PER; i++) {
+        uint32_t p = base + threadIdx.x + i * 256;
+        if (p < end) jump[gb + p] = v[i];
     }
 }
 
@@ -269,8 +337,9 @@ int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounte
 
 int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
 {
-    k_parse<<<bd.B, 32, 0, st>>>(ws.cand, ws.blkN, bd.logS, ws.cost, ws.choice, ws.jump);
-    lc.launches += 1;
+    k_parse<<<bd.B, PARSE_THREADS, 0, st>>>(ws.cand, ws.blkN, bd.logS, ws.cost, ws.choice);
+    k_jump<<<bd.B << (bd.logS - PARSE_CHUNK_LOG), 256, 0, st>>>(ws.blkN, ws.choice, bd.logS, ws.jump);
+    lc.launches += 2;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "salz_cuda: parse_build: %s\n", cudaGetErrorString(e));
