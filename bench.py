@@ -312,9 +312,9 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
 
-    # dominant kernel: k_radix_scatter.  Algorithmic bytes per element per pass =
-    # read key 8 + value 4, write key 8 + value 4 = 24 B.
-    sort_bytes = 24.0 * st["sort_elems"]
+    # dominant kernel: k_scatter (one LSD radix pass).  Algorithmic bytes per element per
+    # pass = read + write of one list element: 16 B packed, 24 B key+value.
+    sort_bytes = float(st["sort_bytes"])
     sort_launches = max(1, st["sort_launches"])
     achieved = sort_bytes / (st["ms_sort"] * 1e-3) / 1e9 if st["ms_sort"] > 0 else 0.0
     traffic = None
@@ -324,7 +324,7 @@ def main():
     except (OSError, ValueError):
         pass
     roofline = {
-        "bound": "hbm", "kernel": "k_radix_scatter", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "bound": "hbm", "kernel": "k_scatter", "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
         "alg_bytes_per_launch": sort_bytes / sort_launches,
         "avg_launch_ms": st["ms_sort"] / sort_launches, "launches": st["sort_launches"],

@@ -34,6 +34,7 @@ typedef struct salz_cuda_stats {
     uint64_t launches;        /* kernels launched */
     uint64_t sort_launches;   /* of which radix scatter passes */
     uint64_t sort_elems;      /* elements moved by the scatter passes (sum over passes) */
+    uint64_t sort_bytes;      /* algorithmic bytes of those passes (16 or 24 B per element) */
     uint64_t doubling_rounds; /* prefix-doubling rounds executed (sum over batches) */
     uint64_t alg_bytes_sa;    /* algorithmic HBM bytes, suffix sorting */
     uint64_t alg_bytes_rest;  /* algorithmic HBM bytes, LCP/ANSV/parse/emit */
@@ -127,8 +128,9 @@ void salz_cuda_host_free(void *p);
 int salz_cuda_get_stats(const salz_cuda_ctx *ctx, salz_cuda_stats *out);
 void salz_cuda_reset_stats(salz_cuda_ctx *ctx);
 
-/* Tunables (tests): mode 0 = two-kernel histogram + scatter, 1 = single-pass
- * decoupled look-back scatter (default). */
+/* Tunables (tests, A/B timing): ranking inside the radix scatter pass.
+ * mode 1 (default) = warp peer masks by shared-memory atomicOr,
+ * mode 0           = warp peer masks by match_any. */
 void salz_cuda_set_sort_mode(salz_cuda_ctx *ctx, int mode);
 
 /* Run this context's copies and kernels on the caller's CUDA stream

@@ -28,7 +28,7 @@ class SalzCudaError(RuntimeError):
 
 class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
-        "blocks", "input_bytes", "output_bytes", "launches", "sort_launches", "sort_elems",
+        "blocks", "input_bytes", "output_bytes", "launches", "sort_launches", "sort_elems", "sort_bytes",
         "doubling_rounds", "alg_bytes_sa", "alg_bytes_rest")] + [(n, C.c_double) for n in (
         "ms_sa", "ms_sort", "ms_lcp", "ms_ansv", "ms_parse", "ms_emit", "ms_total", "ms_h2d", "ms_d2h")]
 

@@ -22,7 +22,6 @@ struct salz_cuda_ctx {
     std::vector<void *> allocs;
     // pinned host mirrors
     uint32_t *h_blkN;
-    uint32_t *h_elemStart;
     uint32_t *h_outLen;
     uint32_t *h_salzLen;
     uint64_t *h_outOff;
@@ -105,15 +104,18 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     for (int i = 0; i < 8 && ok; i++) ok = cudaEventCreate(&c->ev[i]) == cudaSuccess;
     ws.Tcap = M + 256;
     ok = ok && dalloc(c, &ws.T, ws.Tcap);
-    ok = ok && dalloc(c, &ws.blkN, B) && dalloc(c, &ws.elemStart, B + 1);
-    for (int i = 0; i < 2 && ok; i++)
-        ok = dalloc(c, &ws.keys[i], M) && dalloc(c, &ws.vals[i], M) && dalloc(c, &ws.slot[i], M);
-    ok = ok && dalloc(c, &ws.prim, M) && dalloc(c, &ws.rank, M + 64) && dalloc(c, &ws.SA, M + 64);
-    ok = ok && dalloc(c, &ws.hist, 8 * 256) && dalloc(c, &ws.digitBase, 8 * 256);
-    ws.tileStateCap = M / 4096 + 2;
-    ok = ok && dalloc(c, &ws.tileState, ws.tileStateCap * 256) && dalloc(c, &ws.tileCounter, 8);
-    ok = ok && dalloc(c, &ws.tileHist, ws.tileStateCap * 256);
-    ok = ok && dalloc(c, &ws.aggKeep, M / 2048 + 2) && dalloc(c, &ws.aggHead, M / 2048 + 2);
+    ok = ok && dalloc(c, &ws.blkN, B);
+    const bool packed = 3 * logS <= 64;
+    for (int i = 0; i < 2 && ok; i++) {
+        ok = dalloc(c, &ws.keys[i], M) && dalloc(c, &ws.vals[i], packed ? 1 : M);
+        ok = ok && dalloc(c, &ws.listCnt[i], B) && dalloc(c, &ws.listBase[i], B + 1) && dalloc(c, &ws.tileBase[i], B + 1);
+    }
+    ws.tileCap = M / 4096 + B + 2;
+    for (int i = 0; i < 2 && ok; i++) ok = dalloc(c, &ws.tileBlock[i], ws.tileCap);
+    ok = ok && dalloc(c, &ws.rank, M + 64) && dalloc(c, &ws.SA, M + 64);
+    ok = ok && dalloc(c, &ws.hist, B * 8 * 256) && dalloc(c, &ws.digitBase, B * 8 * 256);
+    ok = ok && dalloc(c, &ws.tileState, (ws.tileCap + 1) * 256);
+    ok = ok && dalloc(c, &ws.aggHead, ws.tileCap) && dalloc(c, &ws.aggPst, ws.tileCap) && dalloc(c, &ws.aggKeep, ws.tileCap);
     ok = ok && dalloc(c, &ws.counters, 16);
     ok = ok && dalloc(c, &ws.plcp, M) && dalloc(c, &ws.lcp, M) && dalloc(c, &ws.tileMax, M / 1024 + 1);
     for (int l = 1; l < 6 && ok; l++) {
@@ -132,7 +134,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ok = ok && dalloc(c, &ws.out, ws.outCap);
     ok = ok && cudaMallocHost((void **)&ws.h_counters, 64) == cudaSuccess;
     ok = ok && cudaMallocHost((void **)&c->h_blkN, B * 4) == cudaSuccess;
-    ok = ok && cudaMallocHost((void **)&c->h_elemStart, (B + 1) * 4) == cudaSuccess;
+    ws.h_blkN = c->h_blkN;
     ok = ok && cudaMallocHost((void **)&c->h_outLen, B * 4) == cudaSuccess;
     ok = ok && cudaMallocHost((void **)&c->h_salzLen, B * 4) == cudaSuccess;
     ok = ok && cudaMallocHost((void **)&c->h_outOff, (B + 1) * 8) == cudaSuccess;
@@ -152,7 +154,6 @@ extern "C" void salz_cuda_ctx_destroy(salz_cuda_ctx *c)
     for (void *p : c->allocs) cudaFree(p);
     if (c->ws.h_counters) cudaFreeHost(c->ws.h_counters);
     if (c->h_blkN) cudaFreeHost(c->h_blkN);
-    if (c->h_elemStart) cudaFreeHost(c->h_elemStart);
     if (c->h_outLen) cudaFreeHost(c->h_outLen);
     if (c->h_salzLen) cudaFreeHost(c->h_salzLen);
     if (c->h_outOff) cudaFreeHost(c->h_outOff);
@@ -199,17 +200,14 @@ static int run_batch(salz_cuda_ctx *c, int B, size_t Tstride, int framing, int u
     bd.Tstride = Tstride;
     uint32_t M = 0, maxN = 0;
     for (int b = 0; b < B; b++) {
-        c->h_elemStart[b] = M;
         M += c->h_blkN[b] - 8;
         maxN = std::max(maxN, c->h_blkN[b]);
     }
-    c->h_elemStart[B] = M;
     bd.M = M;
     bd.maxN = maxN;
     CKC(c, cudaMemcpyAsync(ws.blkN, c->h_blkN, (size_t)B * 4, cudaMemcpyHostToDevice, st));
-    CKC(c, cudaMemcpyAsync(ws.elemStart, c->h_elemStart, (size_t)(B + 1) * 4, cudaMemcpyHostToDevice, st));
 
-    LaunchCounter lc = {0, 0, 0};
+    LaunchCounter lc = {0, 0, 0, 0};
     uint64_t algSa = 0;
     int rounds = 0;
     float msSort = 0.f;
@@ -239,6 +237,7 @@ static int run_batch(salz_cuda_ctx *c, int B, size_t Tstride, int framing, int u
     s.launches += lc.launches;
     s.sort_launches += lc.sort_launches;
     s.sort_elems += lc.sort_elems;
+    s.sort_bytes += lc.sort_bytes;
     s.doubling_rounds += rounds;
     s.alg_bytes_sa += algSa;
     if (upto >= 5) {

@@ -198,10 +198,16 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
         } else {
             const int4 *sa = stA[c & 1], *sb = stB[c & 1];
             const uint32_t lastP = min(N - 1, c * PC + PC - 1);
-            for (uint32_t w = (lastP >> 5) + 1; w-- > (c * PC) >> 5;) {
+            const uint32_t firstW = (c * PC) >> 5;
+            int4 na = sa[((lastP | 31u) - lane) & (PC - 1)], nb = sb[((lastP | 31u) - lane) & (PC - 1)];
+            for (uint32_t w = (lastP >> 5) + 1; w-- > firstW;) {
                 const uint32_t q = (w << 5) + 31;
                 const uint32_t p = q - lane;
-                const int4 ra = sa[p & (PC - 1)], rb = sb[p & (PC - 1)];
+                const int4 ra = na, rb = nb;
+                if (w > firstW) {  // next window's records, off the critical path
+                    na = sa[(p - 32) & (PC - 1)];
+                    nb = sb[(p - 32) & (PC - 1)];
+                }
                 const uint32_t l1 = (uint32_t)ra.x, l2 = (uint32_t)rb.x;
                 const int32_t a1 = ra.y, a2 = rb.y;
                 int32_t f1 = SALZ_INF, f2 = SALZ_INF;  // edge weight + final target cost
@@ -216,31 +222,32 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
                     else if (l2 <= (uint32_t)lane) near2 = true;
                     else f2 = a2 + ring[(p + l2) & (2 * PC - 1)];
                 }
-                int32_t x = (p == n) ? 0 : min(f1, f2);  // cost[n] = 0 (ref lib/salz.c:621)
-                const int32_t xfar = x;
+                const int32_t x = (p == n) ? 0 : min(f1, f2);  // cost[n] = 0 (ref lib/salz.c:621)
 
-                // --- fixpoint over in-window edges ---
-                int32_t cst;
-                const unsigned anyNear = __ballot_sync(0xffffffffu, near1 || near2);
-                for (;;) {
-                    // cost[l] = min( min_{k<=l} x[k] + 9(l-k), costRight + 9(l+1) )
-                    int32_t y = x - 9 * lane;
+                // --- literal chain: cost[l] = min( min_{k<=l} x[k] + 9(l-k), costRight + 9(l+1) ) ---
+                int32_t y = x - 9 * lane;
 #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        int32_t t = __shfl_up_sync(0xffffffffu, y, o);
-                        if (lane >= o) y = min(y, t);
+                for (int o = 1; o < 32; o <<= 1) {
+                    int32_t t = __shfl_up_sync(0xffffffffu, y, o);
+                    if (lane >= o) y = min(y, t);
+                }
+                int32_t cst = min(y + 9 * lane, costRight + 9 * (lane + 1));
+                if (p > n) cst = SALZ_INF;
+                // --- in-window edges: relax every edge (factor edges, then one literal
+                // step) until nothing changes; any relaxation order reaches the same
+                // exact fixpoint, and runs of literals after a factor are short ---
+                if (__any_sync(0xffffffffu, near1 || near2)) {
+                    const int s1 = near1 ? (lane - (int)l1) : lane, s2 = near2 ? (lane - (int)l2) : lane;
+                    const int32_t w1 = near1 ? a1 : 0, w2 = near2 ? a2 : 0;
+                    for (;;) {
+                        int32_t v = min(cst, min(w1 + __shfl_sync(0xffffffffu, cst, s1),
+                                                 w2 + __shfl_sync(0xffffffffu, cst, s2)));
+                        int32_t u = __shfl_up_sync(0xffffffffu, v, 1);
+                        if (lane >= 1 && p <= n) v = min(v, u + 9);
+                        const bool changed = v < cst;
+                        cst = v;
+                        if (!__any_sync(0xffffffffu, changed)) break;
                     }
-                    cst = min(y + 9 * lane, costRight + 9 * (lane + 1));
-                    if (p > n) cst = SALZ_INF;
-                    if (!anyNear) break;
-                    int32_t t1 = __shfl_sync(0xffffffffu, cst, near1 ? (lane - (int)l1) : 0);
-                    int32_t t2 = __shfl_sync(0xffffffffu, cst, near2 ? (lane - (int)l2) : 0);
-                    int32_t nx = xfar;
-                    if (near1) nx = min(nx, a1 + t1);
-                    if (near2) nx = min(nx, a2 + t2);
-                    bool changed = nx < x;
-                    x = min(x, nx);
-                    if (!__any_sync(0xffffffffu, changed)) break;
                 }
 
                 // --- choice with the reference's tie-break ---

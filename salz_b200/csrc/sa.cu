@@ -4,27 +4,34 @@
 // 3rdparty/libsais/src/libsais.c:6597-6611).  The suffix array is unique, so
 // any exact suffix sorter yields the same bytes downstream.
 //
-// All blocks of a batch are sorted together.  The sort list holds the suffixes
-// whose final position is not yet known ("unresolved"); it is always ordered by
-// the group they belong to, and group ids are padded global SA slots
-// (b*S + index of the group head), so one global stable LSD radix sort of the
-// packed key (group id, rank of the suffix h positions further) re-sorts every
-// group of every block at once.  Suffixes whose group became a singleton are
-// written to SA and dropped from the list (the list shrinks every round).
+// All blocks of a batch are sorted by the same launches, but every block is
+// its own segment of the sort list: tiles never straddle blocks, digit
+// histograms and look-back chains are per block, so no block-id bits travel
+// in the keys.  The list holds the suffixes whose final position is not yet
+// known; it is always ordered by group, and a group id is the SA slot of the
+// group's first member.  One round:
 //
-// Radix pass = one kernel: per-warp shared-memory digit counters filled with
-// __match_any_sync ranking, decoupled look-back over per-tile digit counts for
-// the global offsets, keys/values staged through shared memory in digit order
-// and written back as coalesced runs.
+//   k_build    key = (group id, 1 + group id of suffix p+h, 0 past the end)
+//   k_scatter  stable LSD radix passes over the key bits (8 bits per pass):
+//              per-warp shared-memory digit counters, ranks from warp-wide
+//              peer masks (shared-memory atomicOr, or match_any), decoupled
+//              look-back over per-tile digit counts, keys staged through
+//              shared memory in digit order and written back as coalesced runs
+//   k_rerank_* adjacent-key compare + scan: new group ids; suffixes whose
+//              group became a singleton are written to SA and dropped
+//
+// Element formats.  PACKED (block capacity S <= 2^21): one u64 per element,
+//   (group:logS | second:logS | p:logS); a pass moves 16 B per element.
+// Otherwise: u64 key (group | second) + u32 value p; 24 B per element.
 #include "salz_dev.cuh"
 
 namespace {
 
-constexpr int SORT_THREADS = 512;
-constexpr int SORT_ITEMS = 8;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr size_t SORT_SMEM = (size_t)SORT_TILE * 12 + (size_t)SORT_WARPS * 256 * 4 + 2 * 256 * 4 + 64;
+constexpr int TT = 512;             // threads per tile CTA
+constexpr int ITEMS = 8;
+constexpr int TILE = TT * ITEMS;    // elements per tile
+constexpr int WARPS = TT / 32;
+constexpr int MAXP = 8;             // radix passes per sort, at most
 
 constexpr uint32_t LB_AGG = 1u << 30;   // tile aggregate published
 constexpr uint32_t LB_INCL = 2u << 30;  // inclusive prefix published
@@ -41,9 +48,29 @@ __device__ __forceinline__ void st_relaxed(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// The sort list of one round: per-block segments cut into tiles.
+struct ListView {
+    const uint32_t *cnt;        // [B]   elements of block b in the list
+    const uint32_t *base;       // [B+1] list offset of block b
+    const uint32_t *tileBase;   // [B+1] first tile of block b
+    const uint32_t *tileBlock;  // [tiles] block of tile t
+};
+
+struct TileLoc { uint32_t b, lt, first, valid; };
+
+__device__ __forceinline__ TileLoc locate(const ListView &lv, uint32_t tile)
+{
+    TileLoc t;
+    t.b = lv.tileBlock[tile];
+    t.lt = tile - lv.tileBase[t.b];
+    t.first = lv.base[t.b] + t.lt * TILE;
+    t.valid = min((uint32_t)TILE, lv.cnt[t.b] - t.lt * TILE);
+    return t;
+}
+
 // Exclusive sum scan over the values held by threads 0..255 (others pass 0).
 // Must be called by every thread of the CTA.  scratch: >= 9 uint32 in smem.
-__device__ __forceinline__ uint32_t excl_scan_first256(uint32_t v, uint32_t *scratch, uint32_t *total)
+__device__ __forceinline__ uint32_t excl_scan_first256(uint32_t v, uint32_t *scratch)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t inc = v;
@@ -57,210 +84,232 @@ __device__ __forceinline__ uint32_t excl_scan_first256(uint32_t v, uint32_t *scr
     if (tid == 0) {
         uint32_t s = 0;
         for (int w = 0; w < 8; w++) { uint32_t c = scratch[w]; scratch[w] = s; s += c; }
-        scratch[8] = s;
     }
     __syncthreads();
     uint32_t r = (warp < 8) ? (scratch[warp] + inc - v) : 0;
-    if (total) *total = scratch[8];
     __syncthreads();
     return r;
 }
 
-// Adds the digits of `key` for passes [0,passes) to shared histograms, one
-// shared atomic per distinct digit per warp.
-__device__ __forceinline__ void hist_add(uint32_t *sh, uint64_t key, int passes, bool valid)
+// ---- list bookkeeping --------------------------------------------------------
+
+// cnt[b] = n_b for the first round.
+__global__ void k_first_counts(const uint32_t *__restrict__ blkN, int B, uint32_t *__restrict__ cnt)
 {
-    const int lane = threadIdx.x & 31;
-    unsigned act = __ballot_sync(0xffffffffu, valid);
-    if (!valid) return;
-    for (int ps = 0; ps < passes; ps++) {
-        uint32_t d = (uint32_t)(key >> (8 * ps)) & 255u;
-        unsigned m = __match_any_sync(act, d);
-        if (lane == __ffs(m) - 1) atomicAdd(&sh[ps * 256 + d], (uint32_t)__popc(m));
-    }
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < B) cnt[b] = blkN[b] - 8;
 }
 
-__device__ __forceinline__ int find_block(const uint32_t *elemStart, int B, uint32_t e)
+// Single CTA: base / tileBase = exclusive prefixes of cnt / tiles(cnt);
+// counters[0] = list length, counters[1] = tiles.
+__global__ void __launch_bounds__(1024) k_tilemap(const uint32_t *__restrict__ cnt, int B, uint32_t *__restrict__ base,
+                                                  uint32_t *__restrict__ tileBase, uint32_t *__restrict__ counters)
 {
-    int lo = 0, hi = B;  // largest b with elemStart[b] <= e
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (elemStart[mid] <= e) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-// Round 0: key = (block id, first h0 bytes big-endian, zero padded past n_b).
-// Elements of a block are emitted in DESCENDING text position so that the
-// stable sort leaves zero-padded ties (only the last < h0 suffixes of a block
-// can be involved) in their correct order: shorter suffix first.
-__global__ void __launch_bounds__(256) k_init_keys(const uint8_t *__restrict__ T, size_t Tstride,
-                                                   const uint32_t *__restrict__ blkN,
-                                                   const uint32_t *__restrict__ elemStart, int B, int logS,
-                                                   int h0, int passes, uint32_t M,
-                                                   uint64_t *__restrict__ keys, uint32_t *__restrict__ vals,
-                                                   uint32_t *__restrict__ slots, uint32_t *__restrict__ hist)
-{
-    __shared__ uint32_t sh[8 * 256];
-    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) sh[i] = 0;
+    __shared__ uint32_t pc[1024], pt[1024];
+    const int tid = threadIdx.x;
+    const int per = (B + 1023) / 1024;
+    const int lo = min(B, tid * per), hi = min(B, lo + per);
+    uint32_t sc = 0, stl = 0;
+    for (int b = lo; b < hi; b++) { uint32_t c = cnt[b]; sc += c; stl += (c + TILE - 1) / TILE; }
+    pc[tid] = sc;
+    pt[tid] = stl;
     __syncthreads();
-    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    bool valid = e < M;
-    uint64_t key = 0;
-    if (valid) {
-        int b = find_block(elemStart, B, e);
-        uint32_t r = e - elemStart[b];
-        uint32_t n = blkN[b] - 8;
-        uint32_t p = n - 1 - r;
-        uint64_t le = load_u64_unaligned(T + (size_t)b * Tstride + p);
-        uint64_t be = __byte_perm((uint32_t)(le >> 32), 0, 0x0123) |
-                      ((uint64_t)__byte_perm((uint32_t)le, 0, 0x0123) << 32);
-        uint32_t have = n - p;  // bytes of the suffix
-        if (have < 8) be &= ~0ull << (8 * (8 - have));
-        uint64_t chars = (h0 == 8) ? be : (be >> (8 * (8 - h0)));
-        key = chars | ((h0 == 8) ? 0ull : ((uint64_t)b << (8 * h0)));
-        keys[e] = key;
-        vals[e] = ((uint32_t)b << logS) | p;
-        slots[e] = ((uint32_t)b << logS) | r;
-    }
-    hist_add(sh, key, passes, valid);
-    __syncthreads();
-    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x)
-        if (sh[i]) atomicAdd(&hist[i], sh[i]);
-}
-
-// Doubling round: key = (group id << logS) | (1 + local rank of suffix p+h, 0 past the end).
-__global__ void __launch_bounds__(256) k_build_keys(const uint32_t *__restrict__ vals,
-                                                    const uint32_t *__restrict__ prim,
-                                                    const uint32_t *__restrict__ rank,
-                                                    const uint32_t *__restrict__ blkN, int logS, uint32_t h,
-                                                    int passes, uint32_t count, uint64_t *__restrict__ keys,
-                                                    uint32_t *__restrict__ hist)
-{
-    __shared__ uint32_t sh[8 * 256];
-    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x) sh[i] = 0;
-    __syncthreads();
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    bool valid = k < count;
-    uint64_t key = 0;
-    if (valid) {
-        uint32_t g = vals[k];
-        uint32_t Smask = (1u << logS) - 1;
-        uint32_t b = g >> logS, p = g & Smask;
-        uint32_t n = blkN[b] - 8;
-        uint32_t sec = 0;
-        if (p + h < n) sec = (rank[g + h] & Smask) + 1;
-        key = ((uint64_t)prim[k] << logS) | sec;
-        keys[k] = key;
-    }
-    hist_add(sh, key, passes, valid);
-    __syncthreads();
-    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x)
-        if (sh[i]) atomicAdd(&hist[i], sh[i]);
-}
-
-// digitBase[pass][d] = exclusive scan of hist[pass][*]
-__global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digitBase)
-{
-    __shared__ uint32_t scratch[16];
-    uint32_t v = hist[blockIdx.x * 256 + threadIdx.x];
-    uint32_t ex = excl_scan_first256(v, scratch, nullptr);
-    digitBase[blockIdx.x * 256 + threadIdx.x] = ex;
-}
-
-// ---- fallback (mode 0): per-tile histograms + serial scan -------------------
-__global__ void __launch_bounds__(256) k_tile_hist(const uint64_t *__restrict__ keys, uint32_t count, int shift,
-                                                   uint32_t *__restrict__ tileHist)
-{
-    __shared__ uint32_t sh[256];
-    sh[threadIdx.x] = 0;
-    __syncthreads();
-    uint32_t base = blockIdx.x * SORT_TILE;
-    for (int i = threadIdx.x; i < SORT_TILE; i += 256) {
-        uint32_t k = base + i;
-        if (k < count) atomicAdd(&sh[(uint32_t)(keys[k] >> shift) & 255u], 1u);
-    }
-    __syncthreads();
-    tileHist[(size_t)blockIdx.x * 256 + threadIdx.x] = sh[threadIdx.x];
-}
-
-// tileHist[t][d] -> exclusive prefix over tiles; digitBase[d] = exclusive scan of totals
-__global__ void __launch_bounds__(256) k_scan_tile_hist(uint32_t *__restrict__ tileHist, uint32_t tiles,
-                                                        uint32_t *__restrict__ digitBase)
-{
-    __shared__ uint32_t scratch[16];
-    uint32_t sum = 0;
-    for (uint32_t t = 0; t < tiles; t++) {
-        uint32_t c = tileHist[(size_t)t * 256 + threadIdx.x];
-        tileHist[(size_t)t * 256 + threadIdx.x] = sum;
-        sum += c;
-    }
-    uint32_t ex = excl_scan_first256(sum, scratch, nullptr);
-    digitBase[threadIdx.x] = ex;
-}
-
-// ---- the radix scatter pass --------------------------------------------------
-// tileOffsets == nullptr : decoupled look-back over tileState (tile ids handed
-//                          out by an atomic ticket so predecessors are running)
-// tileOffsets != nullptr : offsets precomputed by k_scan_tile_hist
-__global__ void __launch_bounds__(SORT_THREADS, 2)
-k_radix_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn,
-                uint64_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut, uint32_t count, int shift,
-                const uint32_t *__restrict__ digitBase, uint32_t *tileState, uint32_t *tileCounter,
-                const uint32_t *__restrict__ tileOffsets)
-{
-    extern __shared__ __align__(16) uint8_t smem[];
-    uint64_t *skeys = (uint64_t *)smem;
-    uint32_t *svals = (uint32_t *)(skeys + SORT_TILE);
-    uint32_t *wcnt = svals + SORT_TILE;           // [SORT_WARPS][256]
-    uint32_t *dstart = wcnt + SORT_WARPS * 256;   // [256]
-    uint32_t *gbase = dstart + 256;               // [256]
-    uint32_t *scratch = gbase + 256;              // [16]
-    __shared__ uint32_t s_tile;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint32_t tile;
-    if (tileOffsets == nullptr) {
-        if (tid == 0) s_tile = atomicAdd(tileCounter, 1u);
-        __syncthreads();
-        tile = s_tile;
-    } else {
-        tile = blockIdx.x;
-    }
-    const uint32_t base = tile * SORT_TILE;
-    const uint32_t valid = min((uint32_t)SORT_TILE, count - base);
-
-    for (int i = tid; i < SORT_WARPS * 256; i += SORT_THREADS) wcnt[i] = 0;
-
-    uint64_t key[SORT_ITEMS];
-    uint32_t val[SORT_ITEMS];
+    if (tid < 32) {  // 1024 partials: each lane scans 32 of them, then a warp scan
+        uint32_t a = 0, t = 0;
+        for (int i = 0; i < 32; i++) { a += pc[tid * 32 + i]; t += pt[tid * 32 + i]; }
+        uint32_t ia = a, it = t;
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        uint32_t idx = warp * (32 * SORT_ITEMS) + i * 32 + lane;
-        if (idx < valid) {
-            key[i] = keysIn[base + idx];
-            val[i] = valsIn[base + idx];
-        } else {
-            key[i] = ~0ull;
-            val[i] = 0;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t x = __shfl_up_sync(0xffffffffu, ia, o), y = __shfl_up_sync(0xffffffffu, it, o);
+            if (tid >= o) { ia += x; it += y; }
+        }
+        uint32_t ra = ia - a, rt = it - t;
+        for (int i = 0; i < 32; i++) {
+            uint32_t x = pc[tid * 32 + i], y = pt[tid * 32 + i];
+            pc[tid * 32 + i] = ra; pt[tid * 32 + i] = rt;
+            ra += x; rt += y;
+        }
+        if (tid == 31) { counters[0] = ia; counters[1] = it; base[B] = ia; tileBase[B] = it; }
+    }
+    __syncthreads();
+    sc = pc[tid];
+    stl = pt[tid];
+    for (int b = lo; b < hi; b++) {
+        uint32_t c = cnt[b];
+        base[b] = sc;
+        tileBase[b] = stl;
+        sc += c;
+        stl += (c + TILE - 1) / TILE;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_tilefill(const uint32_t *__restrict__ tileBase, uint32_t *__restrict__ tileBlock)
+{
+    const uint32_t b = blockIdx.x;
+    const uint32_t lo = tileBase[b], hi = tileBase[b + 1];
+    for (uint32_t t = lo + threadIdx.x; t < hi; t += blockDim.x) tileBlock[t] = b;
+}
+
+// ---- key construction -----------------------------------------------------------
+
+__device__ __forceinline__ void hist_flush(const uint32_t *sh, int passes, uint32_t *hist, uint32_t b)
+{
+    for (int i = threadIdx.x; i < passes * 256; i += blockDim.x)
+        if (sh[i]) atomicAdd(&hist[(size_t)b * MAXP * 256 + i], sh[i]);
+}
+
+// Round 0: key field = first `nchars` bytes of the suffix, big-endian, zero padded
+// past n_b.  Elements of a block are emitted in DESCENDING text position so that
+// the stable sort leaves zero-padded ties (only the last < nchars suffixes of a
+// block can be involved) in their correct order: shorter suffix first.
+template <bool PACKED>
+__global__ void __launch_bounds__(TT) k_init(const uint8_t *__restrict__ T, size_t Tstride,
+                                             const uint32_t *__restrict__ blkN, ListView lv, int logS, int nchars,
+                                             uint64_t *__restrict__ keys, uint32_t *__restrict__ vals,
+                                             uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[MAXP * 256];
+    for (int i = threadIdx.x; i < nchars * 256; i += TT) sh[i] = 0;
+    __syncthreads();
+    const TileLoc tl = locate(lv, blockIdx.x);
+    const uint32_t n = blkN[tl.b] - 8;
+    const uint8_t *Tb = T + (size_t)tl.b * Tstride;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t idx = threadIdx.x + i * TT;
+        if (idx < tl.valid) {
+            const uint32_t p = n - 1 - (tl.lt * TILE + idx);
+            uint64_t le = load_u64_unaligned(Tb + p);
+            uint64_t be = __byte_perm((uint32_t)(le >> 32), 0, 0x0123) |
+                          ((uint64_t)__byte_perm((uint32_t)le, 0, 0x0123) << 32);
+            const uint32_t have = n - p;  // bytes of the suffix
+            if (have < 8) be &= ~0ull << (8 * (8 - have));
+            const uint64_t kf = be >> (8 * (8 - nchars));
+            if (PACKED) {
+                keys[tl.first + idx] = (kf << logS) | p;
+            } else {
+                keys[tl.first + idx] = kf;
+                vals[tl.first + idx] = p;
+            }
+            for (int ps = 0; ps < nchars; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
         }
     }
     __syncthreads();
+    hist_flush(sh, nchars, hist, tl.b);
+}
 
-    uint32_t rnk[SORT_ITEMS];
-    uint32_t *mycnt = wcnt + warp * 256;
+// Doubling round: the list holds (group, -, p); second = 1 + local group id of
+// suffix p+h, 0 past the end.
+template <bool PACKED>
+__global__ void __launch_bounds__(TT) k_build(const uint32_t *__restrict__ rank, const uint32_t *__restrict__ blkN,
+                                              ListView lv, int logS, uint32_t h, int passes,
+                                              uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+                                              uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[MAXP * 256];
+    for (int i = threadIdx.x; i < passes * 256; i += TT) sh[i] = 0;
+    __syncthreads();
+    const TileLoc tl = locate(lv, blockIdx.x);
+    const uint32_t n = blkN[tl.b] - 8;
+    const uint32_t Smask = (1u << logS) - 1;
+    const uint32_t *rk = rank + ((size_t)tl.b << logS);
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-        unsigned m = __match_any_sync(0xffffffffu, d);
-        int leader = __ffs(m) - 1;
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t idx = threadIdx.x + i * TT;
+        if (idx < tl.valid) {
+            const uint64_t e = keys[tl.first + idx];
+            uint32_t p, prim;
+            if (PACKED) { p = (uint32_t)e & Smask; prim = (uint32_t)(e >> (2 * logS)); }
+            else { p = vals[tl.first + idx]; prim = (uint32_t)(e >> logS); }
+            uint32_t sec = 0;
+            if (p + h < n) sec = (rk[p + h] & Smask) + 1;
+            const uint64_t kf = ((uint64_t)prim << logS) | sec;
+            keys[tl.first + idx] = PACKED ? ((kf << logS) | p) : kf;
+            for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
+        }
+    }
+    __syncthreads();
+    hist_flush(sh, passes, hist, tl.b);
+}
+
+// digitBase[b][pass][d] = exclusive scan of hist[b][pass][*].  grid = (passes, B)
+__global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digitBase)
+{
+    __shared__ uint32_t scratch[16];
+    const size_t o = ((size_t)blockIdx.y * MAXP + blockIdx.x) * 256 + threadIdx.x;
+    digitBase[o] = excl_scan_first256(hist[o], scratch);
+}
+
+// ---- the radix scatter pass -------------------------------------------------------
+// Tile ids are handed out by an atomic ticket so that every predecessor in the
+// look-back chain is already running.  tileState[0] is the ticket, the states
+// start at tileState + 256.
+constexpr size_t SCATTER_SMEM_PACKED = (size_t)TILE * 8 + (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 64;
+constexpr size_t SCATTER_SMEM_PAIRS = SCATTER_SMEM_PACKED + (size_t)TILE * 4;
+
+template <bool PACKED, bool MATCH_ANY>
+__global__ void __launch_bounds__(TT, 2)
+k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn, uint64_t *__restrict__ keysOut,
+          uint32_t *__restrict__ valsOut, ListView lv, int shift, int pass, const uint32_t *__restrict__ digitBase,
+          uint32_t *tileState)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint64_t *skeys = (uint64_t *)smem;                 // [TILE]   (phase 2)
+    uint32_t *masks = (uint32_t *)smem;                 // [WARPS][256] (phase 1, aliases skeys)
+    uint32_t *wcnt = (uint32_t *)(skeys + TILE);        // [WARPS][256]
+    uint32_t *dstart = wcnt + WARPS * 256;              // [256]
+    uint32_t *gbase = dstart + 256;                     // [256]
+    uint32_t *scratch = gbase + 256;                    // [16]
+    uint32_t *svals = scratch + 16;                     // [TILE] (pairs only)
+    __shared__ uint32_t s_tile;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(tileState, 1u);
+    for (int i = tid; i < WARPS * 256; i += TT) { wcnt[i] = 0; masks[i] = 0; }
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const TileLoc tl = locate(lv, tile);
+    uint32_t *state = tileState + 256;
+
+    uint64_t key[ITEMS];
+    uint32_t val[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
+        if (idx < tl.valid) {
+            key[i] = keysIn[tl.first + idx];
+            if (!PACKED) val[i] = valsIn[tl.first + idx];
+        } else {
+            key[i] = ~0ull;
+            if (!PACKED) val[i] = 0;
+        }
+    }
+
+    uint32_t rnk[ITEMS];
+    uint32_t *mycnt = wcnt + warp * 256;
+    uint32_t *mymask = masks + warp * 256;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
+        uint32_t m;
+        if (MATCH_ANY) {
+            m = __match_any_sync(0xffffffffu, d);
+        } else {
+            atomicOr(&mymask[d], 1u << lane);
+            __syncwarp();
+            m = mymask[d];
+            __syncwarp();
+        }
+        const int leader = __ffs(m) - 1;
         uint32_t pre = 0;
         if (lane == leader) {
             pre = mycnt[d];
             mycnt[d] = pre + __popc(m);
+            if (!MATCH_ANY) mymask[d] = 0;
         }
         pre = __shfl_sync(0xffffffffu, pre, leader);
-        rnk[i] = pre + __popc(m & ((1u << lane) - 1u));
+        rnk[i] = pre + __popc(m & lt_mask);
         __syncwarp();
     }
     __syncthreads();
@@ -269,237 +318,270 @@ k_radix_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict_
     if (tid < 256) {
         uint32_t sum = 0;
 #pragma unroll
-        for (int w = 0; w < SORT_WARPS; w++) {
+        for (int w = 0; w < WARPS; w++) {
             uint32_t c = wcnt[w * 256 + tid];
             wcnt[w * 256 + tid] = sum;
             sum += c;
         }
         total = sum;
     }
-    uint32_t ex = excl_scan_first256(total, scratch, nullptr);
+    const uint32_t ex = excl_scan_first256(total, scratch);
     if (tid < 256) {
         dstart[tid] = ex;
-        uint32_t cnt = total - ((tid == 255) ? (SORT_TILE - valid) : 0u);
+        const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
         uint32_t prev = 0;
-        if (tileOffsets != nullptr) {
-            prev = tileOffsets[(size_t)tile * 256 + tid];
-        } else if (tile == 0) {
-            st_relaxed(&tileState[tid], LB_INCL | cnt);
+        if (tl.lt == 0) {
+            st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | cnt);
         } else {
-            st_relaxed(&tileState[(size_t)tile * 256 + tid], LB_AGG | cnt);
+            st_relaxed(&state[(size_t)tile * 256 + tid], LB_AGG | cnt);
             for (uint32_t t = tile - 1;; --t) {
                 uint32_t s;
-                do { s = ld_relaxed(&tileState[(size_t)t * 256 + tid]); } while ((s >> 30) == 0);
+                do { s = ld_relaxed(&state[(size_t)t * 256 + tid]); } while ((s >> 30) == 0);
                 prev += s & LB_MASK;
                 if ((s >> 30) == 2) break;
             }
-            st_relaxed(&tileState[(size_t)tile * 256 + tid], LB_INCL | (prev + cnt));
+            st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | (prev + cnt));
         }
-        gbase[tid] = digitBase[tid] + prev - ex;
+        gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pass) * 256 + tid] + prev - ex;
     }
     __syncthreads();
 
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; i++) {
-        uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-        uint32_t pos = dstart[d] + mycnt[d] + rnk[i];
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
+        const uint32_t pos = dstart[d] + mycnt[d] + rnk[i];
         skeys[pos] = key[i];
-        svals[pos] = val[i];
+        if (!PACKED) svals[pos] = val[i];
     }
     __syncthreads();
 
-    for (uint32_t j = tid; j < valid; j += SORT_THREADS) {
-        uint64_t k = skeys[j];
-        uint32_t d = (uint32_t)(k >> shift) & 255u;
-        uint32_t dst = gbase[d] + j;
+    for (uint32_t j = tid; j < tl.valid; j += TT) {
+        const uint64_t k = skeys[j];
+        const uint32_t dst = gbase[(uint32_t)(k >> shift) & 255u] + j;
         keysOut[dst] = k;
-        valsOut[dst] = svals[j];
+        if (!PACKED) valsOut[dst] = svals[j];
     }
 }
 
-}  // namespace
+// ---- re-rank + compaction -------------------------------------------------------------
+// Element k of a block's segment starts a new group ("head") when its key field
+// differs from its predecessor's, or when it is the first of the segment.  From
+// round 1 on a zero second key (suffix ends within h characters) is always a
+// head: two different suffixes of the same group cannot both end inside the
+// compared prefix.  "pst" marks the first element of an OLD group (group field
+// changes); the SA slot of element k is  group(k) + (k - index of its pst),
+// and the new group id is the slot of the element's head.
 
-// ---- re-rank + compaction ----------------------------------------------------
-namespace {
+struct HK { uint32_t head, pst, keep; };  // head/pst: list index + 1 of the last flagged element (0 none)
 
-constexpr int RR_THREADS = 256;
-constexpr int RR_ITEMS = 8;
-constexpr int RR_TILE = RR_THREADS * RR_ITEMS;
-
-// A sorted list element k starts a new group ("head") when its key differs
-// from its predecessor's.  From round 1 on a zero secondary key (suffix ends
-// within h characters) is always a head: two different suffixes of the same
-// group cannot both end inside the compared prefix.
-__device__ __forceinline__ bool is_head(uint64_t prev, uint64_t cur, uint32_t k, uint64_t secMask)
+__device__ __forceinline__ HK hk_combine(HK a, HK b)
 {
-    return k == 0 || prev != cur || (secMask != 0 && (cur & secMask) == 0);
-}
-
-struct HeadKeep { uint32_t head; uint32_t keep; };  // head: slot+1 of last head (0 none)
-
-__device__ __forceinline__ HeadKeep hk_combine(HeadKeep a, HeadKeep b)
-{
-    HeadKeep r;
+    HK r;
     r.head = b.head ? b.head : a.head;
+    r.pst = b.pst ? b.pst : a.pst;
     r.keep = a.keep + b.keep;
     return r;
 }
 
-// Block-wide exclusive scan of HeadKeep over RR_THREADS threads; returns the
-// exclusive prefix for this thread and the block aggregate in *agg.
-__device__ __forceinline__ HeadKeep hk_block_excl(HeadKeep v, HeadKeep *agg, HeadKeep *scratch /*[8+1]*/)
+__device__ __forceinline__ HK hk_block_excl(HK v, HK *agg, HK *scratch /*[WARPS+1]*/)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    HeadKeep inc = v;
+    HK inc = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        HeadKeep t;
+        HK t;
         t.head = __shfl_up_sync(0xffffffffu, inc.head, o);
+        t.pst = __shfl_up_sync(0xffffffffu, inc.pst, o);
         t.keep = __shfl_up_sync(0xffffffffu, inc.keep, o);
         if (lane >= o) inc = hk_combine(t, inc);
     }
     if (lane == 31) scratch[warp] = inc;
     __syncthreads();
     if (tid == 0) {
-        HeadKeep s; s.head = 0; s.keep = 0;
-        for (int w = 0; w < RR_THREADS / 32; w++) {
-            HeadKeep c = scratch[w];
+        HK s = {0, 0, 0};
+        for (int w = 0; w < WARPS; w++) {
+            HK c = scratch[w];
             scratch[w] = s;
             s = hk_combine(s, c);
         }
-        scratch[RR_THREADS / 32] = s;
+        scratch[WARPS] = s;
     }
     __syncthreads();
-    HeadKeep ex;
+    HK ex;
     ex.head = __shfl_up_sync(0xffffffffu, inc.head, 1);
+    ex.pst = __shfl_up_sync(0xffffffffu, inc.pst, 1);
     ex.keep = __shfl_up_sync(0xffffffffu, inc.keep, 1);
-    if (lane == 0) { ex.head = 0; ex.keep = 0; }
+    if (lane == 0) ex = HK{0, 0, 0};
     ex = hk_combine(scratch[warp], ex);
-    *agg = scratch[RR_THREADS / 32];
+    *agg = scratch[WARPS];
     __syncthreads();
     return ex;
 }
 
-// Loads keys[k0-1 .. k0+RR_ITEMS] and returns per-item flags.
-__device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, uint32_t count, uint32_t k0,
-                                           uint64_t secMask, bool head[RR_ITEMS + 1])
+// Flags of the ITEMS elements a thread owns (consecutive), plus head of the next one.
+template <bool PACKED, bool ROUND0>
+__device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, const TileLoc &tl, uint32_t segRemain,
+                                           uint32_t i0, int logS, uint64_t e[ITEMS], bool head[ITEMS + 1],
+                                           bool pst[ITEMS])
 {
-    uint64_t prev = (k0 > 0 && k0 - 1 < count) ? keys[k0 - 1] : 0;
+    // key field and group of an element
+    const uint64_t secMask = ((uint64_t)1 << logS) - 1;
+    auto kf = [&](uint64_t x) -> uint64_t { return PACKED ? (x >> logS) : x; };
+    const bool havePrev = (tl.lt > 0 || i0 > 0) && i0 < tl.valid;
+    uint64_t prev = havePrev ? kf(keys[tl.first + i0 - 1]) : 0;
 #pragma unroll
-    for (int i = 0; i <= RR_ITEMS; i++) {
-        uint32_t k = k0 + i;
-        if (k < count) {
-            uint64_t cur = keys[k];
-            head[i] = is_head(prev, cur, k, secMask);
+    for (int i = 0; i <= ITEMS; i++) {
+        const uint32_t idx = i0 + i;
+        // idx may be one past the tile: still inside the segment when segRemain allows
+        const bool exists = (i < ITEMS) ? (idx < tl.valid) : (idx < tl.valid || (idx == TILE && segRemain > TILE));
+        if (exists) {
+            const uint64_t raw = keys[tl.first + idx];
+            const uint64_t cur = kf(raw);
+            const bool first = (tl.lt == 0 && idx == 0);
+            bool p = first, hd = first || prev != cur;
+            if (!ROUND0) {
+                p = p || (prev >> logS) != (cur >> logS);
+                hd = hd || (cur & secMask) == 0;
+            }
+            head[i] = hd;
+            if (i < ITEMS) { pst[i] = p; e[i] = raw; }
             prev = cur;
         } else {
-            head[i] = true;  // end of list closes the last group
+            head[i] = true;  // end of the segment closes the last group
+            if (i < ITEMS) { pst[i] = false; e[i] = 0; }
         }
     }
 }
 
-__global__ void __launch_bounds__(RR_THREADS) k_rerank_reduce(const uint64_t *__restrict__ keys,
-                                                              const uint32_t *__restrict__ slots, uint32_t count,
-                                                              uint64_t secMask, uint32_t *__restrict__ aggKeep,
-                                                              uint32_t *__restrict__ aggHead)
+template <bool PACKED, bool ROUND0>
+__global__ void __launch_bounds__(TT) k_rerank_reduce(const uint64_t *__restrict__ keys, ListView lv, int logS,
+                                                      uint32_t *__restrict__ aggHead, uint32_t *__restrict__ aggPst,
+                                                      uint32_t *__restrict__ aggKeep)
 {
-    __shared__ HeadKeep scratch[RR_THREADS / 32 + 1];
-    uint32_t k0 = blockIdx.x * RR_TILE + threadIdx.x * RR_ITEMS;
-    bool head[RR_ITEMS + 1];
-    load_flags(keys, count, k0, secMask, head);
-    HeadKeep v; v.head = 0; v.keep = 0;
+    __shared__ HK scratch[WARPS + 1];
+    const TileLoc tl = locate(lv, blockIdx.x);
+    const uint32_t segRemain = lv.cnt[tl.b] - tl.lt * TILE;
+    const uint32_t i0 = threadIdx.x * ITEMS;
+    uint64_t e[ITEMS];
+    bool head[ITEMS + 1], pst[ITEMS];
+    load_flags<PACKED, ROUND0>(keys, tl, segRemain, i0, logS, e, head, pst);
+    HK v = {0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < RR_ITEMS; i++) {
-        uint32_t k = k0 + i;
-        if (k < count) {
-            if (head[i]) v.head = slots[k] + 1;
+    for (int i = 0; i < ITEMS; i++) {
+        if (i0 + i < tl.valid) {
+            const uint32_t k = tl.first + i0 + i;
+            if (head[i]) v.head = k + 1;
+            if (pst[i]) v.pst = k + 1;
             if (!(head[i] && head[i + 1])) v.keep++;
         }
     }
-    HeadKeep agg;
+    HK agg;
     hk_block_excl(v, &agg, scratch);
     if (threadIdx.x == 0) {
-        aggKeep[blockIdx.x] = agg.keep;
         aggHead[blockIdx.x] = agg.head;
+        aggPst[blockIdx.x] = agg.pst;
+        aggKeep[blockIdx.x] = agg.keep;
     }
 }
 
 // Single CTA: exclusive scan of the tile aggregates, in place.
-__global__ void __launch_bounds__(1024) k_rerank_scan(uint32_t *__restrict__ aggKeep, uint32_t *__restrict__ aggHead,
-                                                      uint32_t tiles, uint32_t *__restrict__ counters)
+__global__ void __launch_bounds__(1024) k_rerank_scan(uint32_t *__restrict__ aggHead, uint32_t *__restrict__ aggPst,
+                                                      uint32_t *__restrict__ aggKeep, uint32_t tiles)
 {
-    __shared__ HeadKeep part[1024];
+    __shared__ HK part[1024];
     const int tid = threadIdx.x;
-    uint32_t per = (tiles + 1023) / 1024;
-    uint32_t lo = tid * per, hi = min(tiles, lo + per);
-    HeadKeep s; s.head = 0; s.keep = 0;
-    for (uint32_t t = lo; t < hi; t++) {
-        HeadKeep c; c.head = aggHead[t]; c.keep = aggKeep[t];
-        s = hk_combine(s, c);
-    }
+    const uint32_t per = (tiles + 1023) / 1024;
+    const uint32_t lo = min(tiles, tid * per), hi = min(tiles, lo + per);
+    HK s = {0, 0, 0};
+    for (uint32_t t = lo; t < hi; t++) s = hk_combine(s, HK{aggHead[t], aggPst[t], aggKeep[t]});
     part[tid] = s;
     __syncthreads();
-    if (tid == 0) {
-        HeadKeep run; run.head = 0; run.keep = 0;
-        for (int i = 0; i < 1024; i++) {
-            HeadKeep c = part[i];
-            part[i] = run;
+    if (tid < 32) {
+        HK a = {0, 0, 0};
+        for (int i = 0; i < 32; i++) a = hk_combine(a, part[tid * 32 + i]);
+        HK inc = a;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            HK t;
+            t.head = __shfl_up_sync(0xffffffffu, inc.head, o);
+            t.pst = __shfl_up_sync(0xffffffffu, inc.pst, o);
+            t.keep = __shfl_up_sync(0xffffffffu, inc.keep, o);
+            if (tid >= o) inc = hk_combine(t, inc);
+        }
+        HK run;
+        run.head = __shfl_up_sync(0xffffffffu, inc.head, 1);
+        run.pst = __shfl_up_sync(0xffffffffu, inc.pst, 1);
+        run.keep = __shfl_up_sync(0xffffffffu, inc.keep, 1);
+        if (tid == 0) run = HK{0, 0, 0};
+        for (int i = 0; i < 32; i++) {
+            HK c = part[tid * 32 + i];
+            part[tid * 32 + i] = run;
             run = hk_combine(run, c);
         }
-        counters[0] = run.keep;
     }
     __syncthreads();
     s = part[tid];
     for (uint32_t t = lo; t < hi; t++) {
-        HeadKeep c; c.head = aggHead[t]; c.keep = aggKeep[t];
+        HK c = {aggHead[t], aggPst[t], aggKeep[t]};
         aggHead[t] = s.head;
+        aggPst[t] = s.pst;
         aggKeep[t] = s.keep;
         s = hk_combine(s, c);
     }
 }
 
-__global__ void __launch_bounds__(RR_THREADS) k_rerank_apply(
-    const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals, const uint32_t *__restrict__ slots,
-    uint32_t count, uint64_t secMask, uint32_t Smask, const uint32_t *__restrict__ aggKeep,
-    const uint32_t *__restrict__ aggHead, uint32_t *__restrict__ rank, uint32_t *__restrict__ SA,
-    uint32_t *__restrict__ valsOut, uint32_t *__restrict__ slotsOut, uint32_t *__restrict__ primOut)
+template <bool PACKED, bool ROUND0>
+__global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+                                                     ListView lv, int logS, const uint32_t *__restrict__ aggHead,
+                                                     const uint32_t *__restrict__ aggPst,
+                                                     const uint32_t *__restrict__ aggKeep, uint32_t *__restrict__ rank,
+                                                     uint32_t *__restrict__ SA, uint64_t *__restrict__ keysOut,
+                                                     uint32_t *__restrict__ valsOut, uint32_t *__restrict__ cntNext)
 {
-    __shared__ HeadKeep scratch[RR_THREADS / 32 + 1];
-    uint32_t k0 = blockIdx.x * RR_TILE + threadIdx.x * RR_ITEMS;
-    bool head[RR_ITEMS + 1];
-    load_flags(keys, count, k0, secMask, head);
-    uint32_t sl[RR_ITEMS], vv[RR_ITEMS];
-    HeadKeep v; v.head = 0; v.keep = 0;
+    __shared__ HK scratch[WARPS + 1];
+    const TileLoc tl = locate(lv, blockIdx.x);
+    const uint32_t segRemain = lv.cnt[tl.b] - tl.lt * TILE;
+    const uint32_t i0 = threadIdx.x * ITEMS;
+    const uint32_t Smask = (1u << logS) - 1;
+    uint64_t e[ITEMS];
+    bool head[ITEMS + 1], pst[ITEMS];
+    load_flags<PACKED, ROUND0>(keys, tl, segRemain, i0, logS, e, head, pst);
+    HK v = {0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < RR_ITEMS; i++) {
-        uint32_t k = k0 + i;
-        sl[i] = 0; vv[i] = 0;
-        if (k < count) {
-            sl[i] = slots[k];
-            vv[i] = vals[k];
-            if (head[i]) v.head = sl[i] + 1;
+    for (int i = 0; i < ITEMS; i++) {
+        if (i0 + i < tl.valid) {
+            const uint32_t k = tl.first + i0 + i;
+            if (head[i]) v.head = k + 1;
+            if (pst[i]) v.pst = k + 1;
             if (!(head[i] && head[i + 1])) v.keep++;
         }
     }
-    HeadKeep agg;
-    HeadKeep ex = hk_block_excl(v, &agg, scratch);
-    HeadKeep carry; carry.head = aggHead[blockIdx.x]; carry.keep = aggKeep[blockIdx.x];
-    ex = hk_combine(carry, ex);
-    uint32_t curHead = ex.head;  // slot+1 of the head governing the next element
-    uint32_t outPos = ex.keep;
+    HK agg;
+    HK ex = hk_block_excl(v, &agg, scratch);
+    ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, ex);
+    if (threadIdx.x == 0 && agg.keep) atomicAdd(&cntNext[tl.b], agg.keep);
+    uint32_t curHead = ex.head, curPst = ex.pst, outPos = ex.keep;
+    const size_t gb = (size_t)tl.b << logS;
 #pragma unroll
-    for (int i = 0; i < RR_ITEMS; i++) {
-        uint32_t k = k0 + i;
-        if (k < count) {
-            if (head[i]) curHead = sl[i] + 1;
-            uint32_t r = curHead - 1;
-            rank[vv[i]] = r;
+    for (int i = 0; i < ITEMS; i++) {
+        if (i0 + i < tl.valid) {
+            const uint32_t k = tl.first + i0 + i;
+            if (head[i]) curHead = k + 1;
+            if (pst[i]) curPst = k + 1;
+            uint32_t p, prim;
+            if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
+            else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
+            const uint32_t r = prim + (curHead - curPst);  // SA slot of the group head
+            rank[gb + p] = (uint32_t)gb | r;
             if (head[i] && head[i + 1]) {
-                SA[sl[i]] = vv[i] & Smask;
+                SA[gb + r] = p;
             } else {
-                valsOut[outPos] = vv[i];
-                slotsOut[outPos] = sl[i];
-                primOut[outPos] = r;
+                if (PACKED) {
+                    keysOut[outPos] = ((uint64_t)r << (2 * logS)) | p;
+                } else {
+                    keysOut[outPos] = (uint64_t)r << logS;
+                    valsOut[outPos] = p;
+                }
                 outPos++;
             }
         }
@@ -518,131 +600,170 @@ __global__ void __launch_bounds__(RR_THREADS) k_rerank_apply(
         }                                                                                 \
     } while (0)
 
-static int radix_sort(Workspace &ws, uint32_t count, int passes, int &cur, int mode, cudaStream_t st,
-                      LaunchCounter &lc, cudaEvent_t evA, cudaEvent_t evB, float *msSort)
+namespace {
+
+struct SortCtx {
+    Workspace &ws;
+    const BatchDesc &bd;
+    cudaStream_t st;
+    LaunchCounter &lc;
+    bool packed;
+    int matchAny;
+    int cur;       // keys[cur] holds the list
+    int lcur;      // list view index
+    uint32_t count, tiles;
+};
+
+ListView view(const Workspace &ws, int i)
 {
-    static bool attrSet = false;
-    if (!attrSet) {
-        CK(cudaFuncSetAttribute(k_radix_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SORT_SMEM));
-        attrSet = true;
-    }
-    uint32_t tiles = (count + SORT_TILE - 1) / SORT_TILE;
-    if (msSort) CK(cudaEventRecord(evA, st));
+    ListView lv;
+    lv.cnt = ws.listCnt[i];
+    lv.base = ws.listBase[i];
+    lv.tileBase = ws.tileBase[i];
+    lv.tileBlock = ws.tileBlock[i];
+    return lv;
+}
+
+template <bool PACKED>
+int radix_sort(SortCtx &s, int passes, int shift0)
+{
+    Workspace &ws = s.ws;
+    const size_t smem = PACKED ? SCATTER_SMEM_PACKED : SCATTER_SMEM_PAIRS;
     for (int ps = 0; ps < passes; ps++) {
-        int shift = 8 * ps;
-        if (mode == 1) {
-            CK(cudaMemsetAsync(ws.tileState, 0, (size_t)tiles * 256 * 4, st));
-            CK(cudaMemsetAsync(ws.tileCounter, 0, 4, st));
-            k_radix_scatter<<<tiles, SORT_THREADS, SORT_SMEM, st>>>(
-                ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1], count, shift,
-                ws.digitBase + ps * 256, ws.tileState, ws.tileCounter, nullptr);
-            lc.launches += 1;
-        } else {
-            k_tile_hist<<<tiles, 256, 0, st>>>(ws.keys[cur], count, shift, ws.tileHist);
-            k_scan_tile_hist<<<1, 256, 0, st>>>(ws.tileHist, tiles, ws.digitBase + ps * 256);
-            k_radix_scatter<<<tiles, SORT_THREADS, SORT_SMEM, st>>>(
-                ws.keys[cur], ws.vals[cur], ws.keys[cur ^ 1], ws.vals[cur ^ 1], count, shift,
-                ws.digitBase + ps * 256, nullptr, nullptr, ws.tileHist);
-            lc.launches += 3;
-        }
-        lc.sort_launches += 1;
-        lc.sort_elems += count;
-        cur ^= 1;
-    }
-    if (msSort) {
-        CK(cudaEventRecord(evB, st));
+        CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)s.tiles + 1) * 256 * 4, s.st));
+        if (s.matchAny)
+            k_scatter<PACKED, true><<<s.tiles, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
+                                                                 ws.vals[s.cur ^ 1], view(ws, s.lcur), shift0 + 8 * ps,
+                                                                 ps, ws.digitBase, ws.tileState);
+        else
+            k_scatter<PACKED, false><<<s.tiles, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
+                                                                  ws.vals[s.cur ^ 1], view(ws, s.lcur), shift0 + 8 * ps,
+                                                                  ps, ws.digitBase, ws.tileState);
+        s.lc.launches += 1;
+        s.lc.sort_launches += 1;
+        s.lc.sort_elems += s.count;
+        s.lc.sort_bytes += (uint64_t)s.count * (PACKED ? 16 : 24);
+        s.cur ^= 1;
     }
     CK(cudaGetLastError());
     return 0;
 }
 
-static int rerank(Workspace &ws, uint32_t count, int cur, int slotCur, uint64_t secMask, uint32_t Smask,
-                  cudaStream_t st, LaunchCounter &lc, uint32_t *kept)
+// Re-rank the sorted list, write finished suffixes to SA, compact the rest into
+// the other key buffer and build the next round's list map.
+template <bool PACKED, bool ROUND0>
+int rerank(SortCtx &s)
 {
-    uint32_t tiles = (count + RR_TILE - 1) / RR_TILE;
-    k_rerank_reduce<<<tiles, RR_THREADS, 0, st>>>(ws.keys[cur], ws.slot[slotCur], count, secMask, ws.aggKeep,
-                                                  ws.aggHead);
-    k_rerank_scan<<<1, 1024, 0, st>>>(ws.aggKeep, ws.aggHead, tiles, ws.counters);
-    // compacted values go to the other vals buffer (the sort's scratch side)
-    k_rerank_apply<<<tiles, RR_THREADS, 0, st>>>(ws.keys[cur], ws.vals[cur], ws.slot[slotCur], count, secMask,
-                                                 Smask, ws.aggKeep, ws.aggHead, ws.rank, ws.SA, ws.vals[cur ^ 1],
-                                                 ws.slot[slotCur ^ 1], ws.prim);
-    lc.launches += 3;
-    CK(cudaMemcpyAsync(ws.h_counters, ws.counters, 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    *kept = ws.h_counters[0];
+    Workspace &ws = s.ws;
+    const int logS = s.bd.logS;
+    const int nxt = s.lcur ^ 1;
+    const ListView lv = view(ws, s.lcur);
+    k_rerank_reduce<PACKED, ROUND0><<<s.tiles, TT, 0, s.st>>>(ws.keys[s.cur], lv, logS, ws.aggHead, ws.aggPst, ws.aggKeep);
+    k_rerank_scan<<<1, 1024, 0, s.st>>>(ws.aggHead, ws.aggPst, ws.aggKeep, s.tiles);
+    CK(cudaMemsetAsync(ws.listCnt[nxt], 0, (size_t)s.bd.B * 4, s.st));
+    k_rerank_apply<PACKED, ROUND0><<<s.tiles, TT, 0, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], lv, logS, ws.aggHead,
+                                                             ws.aggPst, ws.aggKeep, ws.rank, ws.SA, ws.keys[s.cur ^ 1],
+                                                             ws.vals[s.cur ^ 1], ws.listCnt[nxt]);
+    k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[nxt], s.bd.B, ws.listBase[nxt], ws.tileBase[nxt], ws.counters);
+    k_tilefill<<<s.bd.B, 128, 0, s.st>>>(ws.tileBase[nxt], ws.tileBlock[nxt]);
+    s.lc.launches += 5;
+    CK(cudaMemcpyAsync(ws.h_counters, ws.counters, 8, cudaMemcpyDeviceToHost, s.st));
+    CK(cudaStreamSynchronize(s.st));
+    s.count = ws.h_counters[0];
+    s.tiles = ws.h_counters[1];
+    s.cur ^= 1;  // compacted list was written to the other buffer
+    s.lcur = nxt;
     return 0;
 }
 
-static int ceil_log2_u64(uint64_t v)
+template <bool PACKED>
+int sa_build_t(SortCtx &s, uint64_t &algBytes, int &rounds, float *msSort, cudaEvent_t evA, cudaEvent_t evB)
 {
-    int l = 0;
-    while ((1ull << l) < v) l++;
-    return l;
+    Workspace &ws = s.ws;
+    const BatchDesc &bd = s.bd;
+    const int logS = bd.logS;
+    static bool attrSet = false;
+    if (!attrSet) {
+        CK(cudaFuncSetAttribute(k_scatter<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
+        CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
+        CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+        CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+        attrSet = true;
+    }
+    const int elemBytes = PACKED ? 8 : 12;
+    int nchars = (2 * logS) / 8;
+    if (nchars > 8) nchars = 8;
+    const int passesD = (2 * logS + 7) / 8;
+    const int shift0 = PACKED ? logS : 0;
+    const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
+
+    // round 0
+    k_first_counts<<<(bd.B + 255) / 256, 256, 0, s.st>>>(ws.blkN, bd.B, ws.listCnt[0]);
+    k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[0], bd.B, ws.listBase[0], ws.tileBase[0], ws.counters);
+    k_tilefill<<<bd.B, 128, 0, s.st>>>(ws.tileBase[0], ws.tileBlock[0]);
+    CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
+    k_init<PACKED><<<s.tiles, TT, 0, s.st>>>(ws.T, bd.Tstride, ws.blkN, view(ws, 0), logS, nchars, ws.keys[0], ws.vals[0],
+                                             ws.hist);
+    k_scan_hist<<<dim3(nchars, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+    s.lc.launches += 5;
+    algBytes += (uint64_t)s.count * (1 + elemBytes);
+    if (msSort) CK(cudaEventRecord(evA, s.st));
+    if (radix_sort<PACKED>(s, nchars, shift0)) return -1;
+    if (msSort) CK(cudaEventRecord(evB, s.st));
+    algBytes += (uint64_t)s.count * 2 * elemBytes * nchars;
+    uint32_t before = s.count;
+    if (rerank<PACKED, true>(s)) return -1;
+    if (msSort) { float ms; CK(cudaEventElapsedTime(&ms, evA, evB)); *msSort += ms; }
+    algBytes += (uint64_t)before * (2 * elemBytes + 4) + (uint64_t)s.count * elemBytes;
+
+    rounds = 0;
+    uint64_t h = (uint64_t)nchars;
+    while (s.count > 0) {
+        if (h >= bd.S) {
+            fprintf(stderr, "salz_cuda: prefix doubling failed to converge (h=%llu)\n", (unsigned long long)h);
+            return -1;
+        }
+        CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
+        k_build<PACKED><<<s.tiles, TT, 0, s.st>>>(ws.rank, ws.blkN, view(ws, s.lcur), logS, (uint32_t)h, passesD,
+                                                  ws.keys[s.cur], ws.vals[s.cur], ws.hist);
+        k_scan_hist<<<dim3(passesD, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+        s.lc.launches += 2;
+        algBytes += (uint64_t)s.count * (2 * elemBytes + 4);
+        if (msSort) CK(cudaEventRecord(evA, s.st));
+        if (radix_sort<PACKED>(s, passesD, shift0)) return -1;
+        if (msSort) CK(cudaEventRecord(evB, s.st));
+        algBytes += (uint64_t)s.count * 2 * elemBytes * passesD;
+        before = s.count;
+        if (rerank<PACKED, false>(s)) return -1;
+        if (msSort) { float ms; CK(cudaEventElapsedTime(&ms, evA, evB)); *msSort += ms; }
+        algBytes += (uint64_t)before * (2 * elemBytes + 4) + (uint64_t)s.count * elemBytes;
+        h *= 2;
+        rounds++;
+    }
+    CK(cudaGetLastError());
+    return 0;
 }
+
+}  // namespace
 
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st, LaunchCounter &lc,
              uint64_t &algBytes, int &rounds, float *msSort)
 {
-    const uint32_t M = bd.M;
-    if (M == 0) return 0;
+    if (bd.M == 0) return 0;
     cudaEvent_t evA = nullptr, evB = nullptr;
     if (msSort) {
         CK(cudaEventCreate(&evA));
         CK(cudaEventCreate(&evB));
         *msSort = 0.f;
     }
-    int bbits = ceil_log2_u64((uint64_t)bd.B);
-    int h0 = (64 - bbits) / 8;
-    if (h0 > 8) h0 = 8;
-    int passes0 = (h0 * 8 + bbits + 7) / 8;
-    int passesD = (2 * bd.logS + bbits + 7) / 8;
-    const uint32_t Smask = bd.S - 1;
-
-    CK(cudaMemsetAsync(ws.hist, 0, 8 * 256 * 4, st));
-    k_init_keys<<<(M + 255) / 256, 256, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.elemStart, bd.B, bd.logS, h0,
-                                                  passes0, M, ws.keys[0], ws.vals[0], ws.slot[0], ws.hist);
-    k_scan_hist<<<passes0, 256, 0, st>>>(ws.hist, ws.digitBase);
-    lc.launches += 2;
-    algBytes += (uint64_t)M * (1 + 8 + 4 + 4);
-    int cur = 0, slotCur = 0;
-    if (radix_sort(ws, M, passes0, cur, sortMode, st, lc, evA, evB, msSort)) return -1;
-    algBytes += (uint64_t)M * 24 * passes0;
-    uint32_t kept = 0;
-    if (rerank(ws, M, cur, slotCur, 0, Smask, st, lc, &kept)) return -1;
-    if (msSort) { float ms; CK(cudaEventElapsedTime(&ms, evA, evB)); *msSort += ms; }
-    algBytes += (uint64_t)M * (8 + 16 + 8) + (uint64_t)kept * 12;
-    cur ^= 1;      // compacted vals were written to the other buffer
-    slotCur ^= 1;
-    rounds = 0;
-    uint64_t h = (uint64_t)h0;
-    const uint64_t secMask = ((uint64_t)1 << bd.logS) - 1;
-    while (kept > 0) {
-        uint32_t count = kept;
-        if (h >= bd.S) {
-            fprintf(stderr, "salz_cuda: prefix doubling failed to converge (h=%llu)\n", (unsigned long long)h);
-            return -1;
-        }
-        CK(cudaMemsetAsync(ws.hist, 0, 8 * 256 * 4, st));
-        k_build_keys<<<(count + 255) / 256, 256, 0, st>>>(ws.vals[cur], ws.prim, ws.rank, ws.blkN, bd.logS,
-                                                          (uint32_t)h, passesD, count, ws.keys[cur], ws.hist);
-        k_scan_hist<<<passesD, 256, 0, st>>>(ws.hist, ws.digitBase);
-        lc.launches += 2;
-        algBytes += (uint64_t)count * 20;
-        if (radix_sort(ws, count, passesD, cur, sortMode, st, lc, evA, evB, msSort)) return -1;
-        algBytes += (uint64_t)count * 24 * passesD;
-        if (rerank(ws, count, cur, slotCur, secMask, Smask, st, lc, &kept)) return -1;
-        if (msSort) { float ms; CK(cudaEventElapsedTime(&ms, evA, evB)); *msSort += ms; }
-        algBytes += (uint64_t)count * (8 + 16 + 8) + (uint64_t)kept * 12;
-        cur ^= 1;
-        slotCur ^= 1;
-        h *= 2;
-        rounds++;
-    }
+    uint32_t tiles = 0;
+    for (int b = 0; b < bd.B; b++) tiles += (ws.h_blkN[b] - 8 + TILE - 1) / TILE;
+    SortCtx s = {ws, bd, st, lc, 3 * bd.logS <= 64, sortMode == 0, 0, 0, bd.M, tiles};
+    int rc = s.packed ? sa_build_t<true>(s, algBytes, rounds, msSort, evA, evB)
+                      : sa_build_t<false>(s, algBytes, rounds, msSort, evA, evB);
     if (msSort) {
         cudaEventDestroy(evA);
         cudaEventDestroy(evB);
     }
-    CK(cudaGetLastError());
-    return 0;
+    return rc;
 }

@@ -32,26 +32,27 @@ struct Workspace {
     uint8_t *T;        // text, Bmax*Tstride + pad
     size_t Tcap;
     uint32_t *blkN;    // [Bmax]   N_b
-    uint32_t *elemStart; // [Bmax+1] prefix of n_b
 
-    // suffix sorting
-    uint64_t *keys[2];
-    uint32_t *vals[2];
-    uint32_t *slot[2];
-    uint32_t *prim;
-    uint32_t *rank;    // [Mcap] by g: padded global slot of the group head / final ISA
-    uint32_t *SA;      // [Mcap] by slot: local text position p
-    uint32_t *hist;    // [8][256] digit histograms for the coming sort
-    uint32_t *digitBase; // [8][256] exclusive scans of hist
-    uint32_t *tileState; // look-back state [tiles][256]
-    size_t tileStateCap; // in tiles
-    uint32_t *tileCounter; // [8] dynamic tile ids per pass
-    uint32_t *tileHist;  // fallback: [tiles][256]
+    // suffix sorting (sa.cu)
+    uint64_t *keys[2];   // [Mcap] list elements (packed) or keys (pairs), double buffered
+    uint32_t *vals[2];   // [Mcap] values of the pairs format (block capacity > 2^21 only)
+    uint32_t *rank;      // [Mcap] by g: padded global slot of the group head / final ISA
+    uint32_t *SA;        // [Mcap] by slot: local text position p
+    uint32_t *listCnt[2];   // [Bmax]   list elements per block
+    uint32_t *listBase[2];  // [Bmax+1] list offset per block
+    uint32_t *tileBase[2];  // [Bmax+1] first tile per block
+    uint32_t *tileBlock[2]; // [tileCap] block of every tile
+    size_t tileCap;
+    uint32_t *hist;      // [Bmax][8][256] digit histograms for the coming sort
+    uint32_t *digitBase; // [Bmax][8][256] exclusive scans of hist
+    uint32_t *tileState; // [1 + tileCap][256]: ticket, then look-back states
     // rerank scans
-    uint32_t *aggKeep;  // [rtiles]
-    uint32_t *aggHead;  // [rtiles]
-    uint32_t *counters; // [16] device scalars: [0]=kept count
+    uint32_t *aggHead;  // [tileCap]
+    uint32_t *aggPst;   // [tileCap]
+    uint32_t *aggKeep;  // [tileCap]
+    uint32_t *counters; // [16] device scalars: [0]=list length, [1]=tiles
     uint32_t *h_counters; // pinned mirror
+    uint32_t *h_blkN;     // pinned host copy of blkN (owned by the context)
 
     // LCP
     int32_t *plcp;     // [Mcap] by g (first V = PLCP+i for irreducible, then PLCP)
@@ -130,7 +131,7 @@ __device__ __forceinline__ int factor_cost_bits(uint32_t offs, uint32_t len)
 }
 
 // ---- host-side launchers (one per pipeline stage) --------------------------
-struct LaunchCounter { uint64_t launches, sort_launches, sort_elems; };
+struct LaunchCounter { uint64_t launches, sort_launches, sort_elems, sort_bytes; };
 
 // sa.cu
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st,
