@@ -110,7 +110,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
         ok = dalloc(c, &ws.keys[i], M) && dalloc(c, &ws.vals[i], packed ? 1 : M);
         ok = ok && dalloc(c, &ws.listCnt[i], B) && dalloc(c, &ws.listBase[i], B + 1) && dalloc(c, &ws.tileBase[i], B + 1);
     }
-    ws.tileCap = M / 4096 + B + 2;
+    ws.tileCap = M / sa_tile_elems() + B + 2;
     for (int i = 0; i < 2 && ok; i++) ok = dalloc(c, &ws.tileBlock[i], ws.tileCap);
     ok = ok && dalloc(c, &ws.rank, M + 64) && dalloc(c, &ws.SA, M + 64);
     ok = ok && dalloc(c, &ws.hist, B * 8 * 256) && dalloc(c, &ws.digitBase, B * 8 * 256);

@@ -27,8 +27,14 @@
 
 namespace {
 
-constexpr int TT = 512;             // threads per tile CTA
-constexpr int ITEMS = 8;
+#ifndef SALZ_TT
+#define SALZ_TT 384
+#endif
+#ifndef SALZ_ITEMS
+#define SALZ_ITEMS 12
+#endif
+constexpr int TT = SALZ_TT;         // threads per tile CTA (>= 256)
+constexpr int ITEMS = SALZ_ITEMS;
 constexpr int TILE = TT * ITEMS;    // elements per tile
 constexpr int WARPS = TT / 32;
 constexpr int MAXP = 8;             // radix passes per sort, at most
@@ -244,20 +250,21 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
 // Tile ids are handed out by an atomic ticket so that every predecessor in the
 // look-back chain is already running.  tileState[0] is the ticket, the states
 // start at tileState + 256.
-constexpr size_t SCATTER_SMEM_PACKED = (size_t)TILE * 8 + (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 64;
+constexpr size_t SCATTER_SMEM_PACKED = (size_t)TILE * 8 + 2 * (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 64;
 constexpr size_t SCATTER_SMEM_PAIRS = SCATTER_SMEM_PACKED + (size_t)TILE * 4;
+constexpr int SCATTER_MIN_CTAS = (TT * ITEMS <= 2048) ? 4 : 2;
 
 template <bool PACKED, bool MATCH_ANY>
-__global__ void __launch_bounds__(TT, 2)
+__global__ void __launch_bounds__(TT, SCATTER_MIN_CTAS)
 k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn, uint64_t *__restrict__ keysOut,
           uint32_t *__restrict__ valsOut, ListView lv, int shift, int pass, const uint32_t *__restrict__ digitBase,
           uint32_t *tileState)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint64_t *skeys = (uint64_t *)smem;                 // [TILE]   (phase 2)
-    uint32_t *masks = (uint32_t *)smem;                 // [WARPS][256] (phase 1, aliases skeys)
-    uint32_t *wcnt = (uint32_t *)(skeys + TILE);        // [WARPS][256]
-    uint32_t *dstart = wcnt + WARPS * 256;              // [256]
+    uint64_t *skeys = (uint64_t *)smem;                 // [TILE] keys in digit order
+    uint32_t *wcnt = (uint32_t *)(skeys + TILE);        // [WARPS][256] per-warp digit counts -> running offsets
+    uint32_t *masks = wcnt + WARPS * 256;               // [WARPS][256] peer masks
+    uint32_t *dstart = masks + WARPS * 256;             // [256]
     uint32_t *gbase = dstart + 256;                     // [256]
     uint32_t *scratch = gbase + 256;                    // [16]
     uint32_t *svals = scratch + 16;                     // [TILE] (pairs only)
@@ -265,7 +272,7 @@ k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ vals
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(tileState, 1u);
-    for (int i = tid; i < WARPS * 256; i += TT) { wcnt[i] = 0; masks[i] = 0; }
+    for (int i = tid; i < 2 * WARPS * 256; i += TT) wcnt[i] = 0;  // counts and masks
     __syncthreads();
     const uint32_t tile = s_tile;
     const TileLoc tl = locate(lv, tile);
@@ -284,9 +291,31 @@ k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ vals
             if (!PACKED) val[i] = 0;
         }
     }
-
-    uint32_t rnk[ITEMS];
+    // early counts: the tile's digit histogram is published before the ranking so
+    // that successors find an inclusive prefix by the time they look back
     uint32_t *mycnt = wcnt + warp * 256;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) atomicAdd(&mycnt[(uint32_t)(key[i] >> shift) & 255u], 1u);
+    __syncthreads();
+
+    uint32_t total = 0;
+    if (tid < 256) {
+        uint32_t sum = 0;
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) {
+            uint32_t c = wcnt[w * 256 + tid];
+            wcnt[w * 256 + tid] = sum;
+            sum += c;
+        }
+        total = sum;
+        const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
+        st_relaxed(&state[(size_t)tile * 256 + tid], (tl.lt == 0 ? LB_INCL : LB_AGG) | cnt);
+    }
+    const uint32_t ex = excl_scan_first256(total, scratch);
+    if (tid < 256) dstart[tid] = ex;
+    __syncthreads();
+
+    // ranking: peers of a lane = lanes of the warp holding the same digit
     uint32_t *mymask = masks + warp * 256;
     const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
@@ -309,49 +338,25 @@ k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ vals
             if (!MATCH_ANY) mymask[d] = 0;
         }
         pre = __shfl_sync(0xffffffffu, pre, leader);
-        rnk[i] = pre + __popc(m & lt_mask);
+        const uint32_t pos = dstart[d] + pre + __popc(m & lt_mask);
+        skeys[pos] = key[i];
+        if (!PACKED) svals[pos] = val[i];
         __syncwarp();
     }
-    __syncthreads();
 
-    uint32_t total = 0;
     if (tid < 256) {
-        uint32_t sum = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; w++) {
-            uint32_t c = wcnt[w * 256 + tid];
-            wcnt[w * 256 + tid] = sum;
-            sum += c;
-        }
-        total = sum;
-    }
-    const uint32_t ex = excl_scan_first256(total, scratch);
-    if (tid < 256) {
-        dstart[tid] = ex;
-        const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
         uint32_t prev = 0;
-        if (tl.lt == 0) {
-            st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | cnt);
-        } else {
-            st_relaxed(&state[(size_t)tile * 256 + tid], LB_AGG | cnt);
+        if (tl.lt != 0) {
             for (uint32_t t = tile - 1;; --t) {
                 uint32_t s;
                 do { s = ld_relaxed(&state[(size_t)t * 256 + tid]); } while ((s >> 30) == 0);
                 prev += s & LB_MASK;
                 if ((s >> 30) == 2) break;
             }
+            const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
             st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | (prev + cnt));
         }
         gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pass) * 256 + tid] + prev - ex;
-    }
-    __syncthreads();
-
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-        const uint32_t pos = dstart[d] + mycnt[d] + rnk[i];
-        skeys[pos] = key[i];
-        if (!PACKED) svals[pos] = val[i];
     }
     __syncthreads();
 
@@ -745,6 +750,8 @@ int sa_build_t(SortCtx &s, uint64_t &algBytes, int &rounds, float *msSort, cudaE
 }
 
 }  // namespace
+
+int sa_tile_elems() { return TILE; }
 
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st, LaunchCounter &lc,
              uint64_t &algBytes, int &rounds, float *msSort)

@@ -134,6 +134,7 @@ __device__ __forceinline__ int factor_cost_bits(uint32_t offs, uint32_t len)
 struct LaunchCounter { uint64_t launches, sort_launches, sort_elems, sort_bytes; };
 
 // sa.cu
+int sa_tile_elems();  // list elements per sort tile
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st,
              LaunchCounter &lc, uint64_t &algBytes, int &rounds, float *msSort);
 // lcp.cu

@@ -27,3 +27,8 @@ for k in sorted(order):
     st = sorted(((int(r[c] or 0), hdr[c][6:]) for c in stall_cols), reverse=True)[:3]
     print("%5d %5.1f%% exec=%-9s %-64s %s" % (k, 100.0 * int(r[si] or 0) / max(1, tot), r[ii], r[1].strip()[:64],
                                             " ".join("%s:%d" % (n, v) for v, n in st if v)))
+agg = {}
+for r in data:
+    for c in stall_cols:
+        agg[hdr[c][6:]] = agg.get(hdr[c][6:], 0) + int(r[c] or 0)
+print("stall totals:", " ".join("%s:%.1f%%" % (k, 100.0 * v / max(1, tot)) for k, v in sorted(agg.items(), key=lambda x: -x[1]) if v))
