@@ -107,7 +107,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ok = ok && dalloc(c, &ws.blkN, B);
     const bool packed = 3 * logS <= 64;
     for (int i = 0; i < 2 && ok; i++) {
-        ok = dalloc(c, &ws.keys[i], M) && dalloc(c, &ws.vals[i], packed ? 1 : M);
+        ok = dalloc(c, &ws.keys[i], M + M / 4096 + 64) && dalloc(c, &ws.vals[i], packed ? 1 : M);  // keys[0] doubles as the ANSV far list
         ok = ok && dalloc(c, &ws.listCnt[i], B) && dalloc(c, &ws.listBase[i], B + 1) && dalloc(c, &ws.tileBase[i], B + 1);
     }
     ws.tileCap = M / sa_tile_elems() + B + 2;

@@ -1,125 +1,11 @@
-// parse.cu - PSV/NSV with match lengths, and the cost-optimal LZ parse.
+// parse.cu - the cost-optimal LZ parse.
 //
-//   k_ansv : for every SA slot r (value v = SA[r]) the nearest slots to the left /
-//            right holding a smaller text position (ref lib/salz.c:471-490), and
-//            the match lengths as range minima of LCP between them
-//            (== lcp_cmp's result, ref lib/salz.c:492-538), written in TEXT order
-//            as (p-psv, psv_len, p-nsv, nsv_len) exactly like the reference's aux
-//            table after factorize() (ref lib/salz.c:540-560).
 //   k_parse: right-to-left shortest-path DP with the reference's cost model and
 //            strict '<' tie-break order literal, PSV, NSV (ref lib/salz.c:562-662).
+//   k_jump : chunk-exit pointers of the chosen parse for the token walk in emit.cu.
 #include "salz_dev.cuh"
 
 namespace {
-
-struct Pyr {
-    const int32_t *sa[6];   // sa[0] = SA (as int32), sa[l] = level-l minima
-    const int32_t *lcp[6];
-    int top;                // coarsest level
-    int logS;
-};
-
-// ---------------------------------------------------------------------------
-// ANSV by walking the min-pyramids.  Level l entry j of block b lives at
-// (b << (logS - 5l)) + j.  Padding entries hold INT_MAX in both pyramids.
-// ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_ansv(Pyr py, const uint32_t *__restrict__ blkN, int4 *__restrict__ cand)
-{
-    const int logS = py.logS;
-    const uint32_t Smask = (1u << logS) - 1;
-    const uint32_t s = blockIdx.x * 256 + threadIdx.x;
-    const uint32_t b = s >> logS, r = s & Smask;
-    const uint32_t n = blkN[b] - 8;
-    if (r >= n) return;
-
-    const int32_t *sa0 = py.sa[0] + ((size_t)b << logS);
-    const int32_t *lcp0 = py.lcp[0] + ((size_t)b << logS);
-    const int32_t v = sa0[r];
-
-    // level-0 accessors honour the n_b bound (slots >= n are uninitialised)
-    auto SAat = [&](int lvl, uint32_t j) -> int32_t {
-        if (lvl == 0) return (j < n) ? sa0[j] : 0x7fffffff;
-        return py.sa[lvl][((size_t)b << (logS - 5 * lvl)) + j];
-    };
-    auto LCPat = [&](int lvl, uint32_t j) -> int32_t {
-        if (lvl == 0) return (j < n) ? lcp0[j] : 0x7fffffff;
-        return py.lcp[lvl][((size_t)b << (logS - 5 * lvl)) + j];
-    };
-
-    // ---- PSV: nearest smaller to the left, min LCP over (r', r] ----
-    int32_t psv = -1, psvLen = 0;
-    {
-        int32_t m = lcp0[r];
-        int lvl = 0;
-        uint32_t pos = r;
-        int fl = -1;
-        uint32_t fj = 0;
-        for (;;) {
-            uint32_t start = pos & ~31u;
-            for (uint32_t j = pos; j-- > start;) {
-                if (SAat(lvl, j) < v) { fl = lvl; fj = j; break; }
-                m = min(m, LCPat(lvl, j));
-            }
-            if (fl >= 0 || lvl == py.top) break;
-            pos >>= 5;
-            lvl++;
-        }
-        if (fl >= 0) {
-            while (fl > 0) {
-                fl--;
-                uint32_t c0 = fj << 5;
-                for (uint32_t c = c0 + 32; c-- > c0;) {
-                    if (SAat(fl, c) < v) { fj = c; break; }
-                    m = min(m, LCPat(fl, c));
-                }
-            }
-            psv = sa0[fj];
-            psvLen = m;
-        }
-    }
-    // ---- NSV: nearest smaller to the right, min LCP over (r, r''] ----
-    int32_t nsv = -1, nsvLen = 0;
-    {
-        int32_t m = 0x7fffffff;
-        int lvl = 0;
-        uint32_t pos = r;
-        int fl = -1;
-        uint32_t fj = 0;
-        for (;;) {
-            uint32_t levelSize = 1u << (logS - 5 * lvl);
-            uint32_t end = min(pos | 31u, levelSize - 1);
-            for (uint32_t j = pos + 1; j <= end; j++) {
-                if (SAat(lvl, j) < v) { fl = lvl; fj = j; break; }
-                m = min(m, LCPat(lvl, j));
-            }
-            if (fl >= 0 || lvl == py.top) break;
-            pos >>= 5;
-            lvl++;
-        }
-        if (fl >= 0) {
-            while (fl > 0) {
-                fl--;
-                uint32_t c0 = fj << 5;
-                for (uint32_t c = c0; c < c0 + 32; c++) {
-                    if (SAat(fl, c) < v) { fj = c; break; }
-                    m = min(m, LCPat(fl, c));
-                }
-            }
-            nsv = sa0[fj];
-            nsvLen = min(m, lcp0[fj]);
-        }
-    }
-    int4 o;
-    if (v == 0) {
-        o = make_int4(-1, 1, -1, 1);  // position 0 is a forced literal (ref lib/salz.c:546-548)
-    } else {
-        o.x = v - psv;   // psv == -1 gives v + 1 like the reference
-        o.y = psvLen;
-        o.z = v - nsv;
-        o.w = nsvLen;
-    }
-    cand[((size_t)b << logS) + (uint32_t)v] = o;
-}
 
 // ---------------------------------------------------------------------------
 // Optimal parse.  One CTA per block: warp 0 is the consumer that walks the
@@ -317,30 +203,6 @@ __global__ void __launch_bounds__(256) k_jump(const uint32_t *__restrict__ blkN,
 }
 
 }  // namespace
-
-int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
-{
-    Pyr py;
-    py.logS = bd.logS;
-    py.sa[0] = (const int32_t *)ws.SA;
-    py.lcp[0] = ws.lcp;
-    int top = 0;
-    while ((bd.S >> (5 * top)) > 32) top++;
-    for (int l = 1; l < 6; l++) {
-        py.sa[l] = ws.pyrSA[l];
-        py.lcp[l] = ws.pyrLCP[l];
-    }
-    py.top = top;
-    const size_t total = (size_t)bd.B * bd.S;
-    k_ansv<<<(uint32_t)(total / 256), 256, 0, st>>>(py, ws.blkN, ws.cand);
-    lc.launches += 1;
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) {
-        fprintf(stderr, "salz_cuda: ansv_build: %s\n", cudaGetErrorString(e));
-        return -1;
-    }
-    return 0;
-}
 
 int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
 {

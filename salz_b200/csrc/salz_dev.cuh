@@ -139,8 +139,9 @@ int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st,
              LaunchCounter &lc, uint64_t &algBytes, int &rounds, float *msSort);
 // lcp.cu
 int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
-// parse.cu
+// ansv.cu
 int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
+// parse.cu
 int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
 // emit.cu
 int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,
