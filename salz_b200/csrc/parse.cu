@@ -8,26 +8,29 @@
 namespace {
 
 // ---------------------------------------------------------------------------
-// Optimal parse.  One CTA per block: warp 0 is the consumer that walks the
-// serial cost chain in 32-position windows right to left, warps 1..3 are
-// producers that stage the next PC-position chunk (candidates, edge weights,
-// and the final costs of targets that lie at least one whole chunk to the
-// right) in shared memory while the consumer works, so the chain never waits
-// on global memory.
+// Optimal parse.  One CTA per block.  Warp 0 is the consumer: it walks the
+// serial cost chain in 32-position windows right to left and does nothing
+// else.  Warps 1..3 work one chunk (PC positions) ahead and one behind it:
+//   stage(c-1)  candidates, edge weights and the final costs of targets that
+//               lie at least one whole chunk to the right of chunk c-1, into
+//               shared memory, so the chain never waits on global memory;
+//   finish(c+1) the choice per position, recomputed from the now final costs
+//               with the reference's comparison order (strict '<': literal,
+//               PSV, NSV; ref lib/salz.c:622-661), and written out.
 //
 // Inside a window lane l owns position q - l (q = right end).  Targets
-//   - at least one chunk ahead of the consumer: weight + cost staged ("far"),
+//   - staged as "far": weight + final cost, ready,
 //   - beyond the window but inside the last two chunks: cost ring in smem,
-//   - inside the window: relaxed to a fixpoint with shuffles (at most ~10
-//     iterations because factors are >= 3 long).
-// The literal chain inside the window is a prefix-min scan in (min,+).  Costs
-// are exact, so the choice is recomputed per lane with the reference's
-// comparison order (strict '<': literal, PSV, NSV; ref lib/salz.c:622-661).
+//   - inside the window: relaxed to a fixpoint with shuffles.
+// The literal chain inside the window is a prefix-min scan in (min,+).
 // ---------------------------------------------------------------------------
 constexpr int PC = 512;            // positions per staged chunk
-constexpr int PARSE_THREADS = 128; // 1 consumer warp + 3 producer warps
+constexpr int PARSE_THREADS = 128; // 1 consumer warp + 3 helper warps
 constexpr int NOT_FAR = -1;
+constexpr size_t PARSE_SMEM = 3 * PC * 2 * sizeof(int4) + 2 * PC * sizeof(int32_t);
 
+// record: x = len (>= 3), y = weight, z = weight + final target cost or NOT_FAR, w = offs.
+// An absent candidate is staged as far with cost INF.
 __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const int32_t *cs, uint32_t n,
                                             uint32_t chunk, int4 *sa, int4 *sb, int tid, int nthreads)
 {
@@ -35,22 +38,18 @@ __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const i
     const uint32_t farFrom = (chunk + 2) * PC;  // targets >= this are final and visible
     for (uint32_t i = tid; i < PC; i += nthreads) {
         const uint32_t p = base + i;
-        int4 a = make_int4(0, 0, NOT_FAR, 0), b = make_int4(0, 0, NOT_FAR, 0);
+        int4 a = make_int4(0, 0, SALZ_INF, 0), b = make_int4(0, 0, SALZ_INF, 0);
         if (p >= 1 && p < n) {
-            int4 c = cd[p];
+            const int4 c = cd[p];
             if (c.y >= 3) {
-                a.x = c.y;
-                a.y = factor_cost_bits((uint32_t)c.x, (uint32_t)c.y);
-                a.w = c.x;
-                uint32_t t = p + (uint32_t)c.y;
-                if (t >= farFrom) a.z = a.y + __ldcg(&cs[t]);
+                const int w = factor_cost_bits((uint32_t)c.x, (uint32_t)c.y);
+                const uint32_t t = p + (uint32_t)c.y;
+                a = make_int4(c.y, w, (t >= farFrom) ? w + __ldcg(&cs[t]) : NOT_FAR, c.x);
             }
             if (c.w >= 3) {
-                b.x = c.w;
-                b.y = factor_cost_bits((uint32_t)c.z, (uint32_t)c.w);
-                b.w = c.z;
-                uint32_t t = p + (uint32_t)c.w;
-                if (t >= farFrom) b.z = b.y + __ldcg(&cs[t]);
+                const int w = factor_cost_bits((uint32_t)c.z, (uint32_t)c.w);
+                const uint32_t t = p + (uint32_t)c.w;
+                b = make_int4(c.w, w, (t >= farFrom) ? w + __ldcg(&cs[t]) : NOT_FAR, c.z);
             }
         }
         sa[i] = a;
@@ -58,12 +57,39 @@ __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const i
     }
 }
 
+// Choices of a chunk whose costs (and every cost to its right) are final.
+__device__ __forceinline__ void finish_chunk(const int4 *sa, const int4 *sb, const int32_t *cs, uint32_t N, uint32_t n,
+                                             uint32_t chunk, int2 *__restrict__ ch, int tid, int nthreads)
+{
+    const uint32_t base = chunk * PC;
+    for (uint32_t i = tid; i < PC; i += nthreads) {
+        const uint32_t p = base + i;
+        if (p >= N) break;
+        uint32_t bo = 0, bl = 1;
+        if (p >= 1 && p < n) {  // position 0 and the 8-byte tail are forced literals
+            const int4 a = sa[i], b = sb[i];
+            int32_t best = 9 + __ldcg(&cs[p + 1]);
+            if (a.z != SALZ_INF) {
+                const int32_t c1 = (a.z != NOT_FAR) ? a.z : a.y + __ldcg(&cs[p + (uint32_t)a.x]);
+                if (c1 < best) { best = c1; bo = (uint32_t)a.w; bl = (uint32_t)a.x; }
+            }
+            if (b.z != SALZ_INF) {
+                const int32_t c2 = (b.z != NOT_FAR) ? b.z : b.y + __ldcg(&cs[p + (uint32_t)b.x]);
+                if (c2 < best) { best = c2; bo = (uint32_t)b.w; bl = (uint32_t)b.x; }
+            }
+        }
+        ch[p] = make_int2((int)bo, (int)bl);
+    }
+}
+
 __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict__ cand,
                                                          const uint32_t *__restrict__ blkN, int logS, int32_t *cost,
                                                          int2 *__restrict__ choice)
 {
-    __shared__ int4 stA[2][PC], stB[2][PC];
-    __shared__ int32_t ring[2 * PC];
+    extern __shared__ __align__(16) uint8_t psmem[];
+    int4 *stA = (int4 *)psmem;            // [3][PC]
+    int4 *stB = stA + 3 * PC;             // [3][PC]
+    int32_t *ring = (int32_t *)(stB + 3 * PC);  // [2 * PC]
     const uint32_t b = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t N = blkN[b];
@@ -74,15 +100,23 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
     int2 *ch = choice + gb;
 
     const uint32_t nChunks = (N + PC - 1) / PC;
-    stage_chunk(cd, cs, n, nChunks - 1, stA[(nChunks - 1) & 1], stB[(nChunks - 1) & 1], tid, PARSE_THREADS);
+    {
+        const uint32_t c = nChunks - 1;
+        stage_chunk(cd, cs, n, c, stA + (c % 3) * PC, stB + (c % 3) * PC, tid, PARSE_THREADS);
+    }
     __syncthreads();
 
     int32_t costRight = SALZ_INF;  // cost[q+1] of the window being processed
     for (uint32_t c = nChunks; c-- > 0;) {
         if (warp != 0) {
-            if (c > 0) stage_chunk(cd, cs, n, c - 1, stA[(c - 1) & 1], stB[(c - 1) & 1], tid - 32, PARSE_THREADS - 32);
+            if (c + 1 < nChunks)
+                finish_chunk(stA + ((c + 1) % 3) * PC, stB + ((c + 1) % 3) * PC, cs, N, n, c + 1, ch, tid - 32,
+                             PARSE_THREADS - 32);
+            if (c > 0)
+                stage_chunk(cd, cs, n, c - 1, stA + ((c - 1) % 3) * PC, stB + ((c - 1) % 3) * PC, tid - 32,
+                            PARSE_THREADS - 32);
         } else {
-            const int4 *sa = stA[c & 1], *sb = stB[c & 1];
+            const int4 *sa = stA + (c % 3) * PC, *sb = stB + (c % 3) * PC;
             const uint32_t lastP = min(N - 1, c * PC + PC - 1);
             const uint32_t firstW = (c * PC) >> 5;
             int4 na = sa[((lastP | 31u) - lane) & (PC - 1)], nb = sb[((lastP | 31u) - lane) & (PC - 1)];
@@ -94,20 +128,12 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
                     na = sa[(p - 32) & (PC - 1)];
                     nb = sb[(p - 32) & (PC - 1)];
                 }
-                const uint32_t l1 = (uint32_t)ra.x, l2 = (uint32_t)rb.x;
-                const int32_t a1 = ra.y, a2 = rb.y;
-                int32_t f1 = SALZ_INF, f2 = SALZ_INF;  // edge weight + final target cost
-                bool near1 = false, near2 = false;
-                if (l1 >= 3) {
-                    if (ra.z != NOT_FAR) f1 = ra.z;
-                    else if (l1 <= (uint32_t)lane) near1 = true;
-                    else f1 = a1 + ring[(p + l1) & (2 * PC - 1)];
-                }
-                if (l2 >= 3) {
-                    if (rb.z != NOT_FAR) f2 = rb.z;
-                    else if (l2 <= (uint32_t)lane) near2 = true;
-                    else f2 = a2 + ring[(p + l2) & (2 * PC - 1)];
-                }
+                const int32_t rv1 = ring[(p + (uint32_t)ra.x) & (2 * PC - 1)];
+                const int32_t rv2 = ring[(p + (uint32_t)rb.x) & (2 * PC - 1)];
+                const bool near1 = ra.z == NOT_FAR && ra.x <= lane;
+                const bool near2 = rb.z == NOT_FAR && rb.x <= lane;
+                const int32_t f1 = (ra.z != NOT_FAR) ? ra.z : (near1 ? SALZ_INF : ra.y + rv1);
+                const int32_t f2 = (rb.z != NOT_FAR) ? rb.z : (near2 ? SALZ_INF : rb.y + rv2);
                 const int32_t x = (p == n) ? 0 : min(f1, f2);  // cost[n] = 0 (ref lib/salz.c:621)
 
                 // --- literal chain: cost[l] = min( min_{k<=l} x[k] + 9(l-k), costRight + 9(l+1) ) ---
@@ -123,8 +149,8 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
                 // step) until nothing changes; any relaxation order reaches the same
                 // exact fixpoint, and runs of literals after a factor are short ---
                 if (__any_sync(0xffffffffu, near1 || near2)) {
-                    const int s1 = near1 ? (lane - (int)l1) : lane, s2 = near2 ? (lane - (int)l2) : lane;
-                    const int32_t w1 = near1 ? a1 : 0, w2 = near2 ? a2 : 0;
+                    const int s1 = near1 ? (lane - ra.x) : lane, s2 = near2 ? (lane - rb.x) : lane;
+                    const int32_t w1 = near1 ? ra.y : 0, w2 = near2 ? rb.y : 0;
                     for (;;) {
                         int32_t v = min(cst, min(w1 + __shfl_sync(0xffffffffu, cst, s1),
                                                  w2 + __shfl_sync(0xffffffffu, cst, s2)));
@@ -135,31 +161,15 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
                         if (!__any_sync(0xffffffffu, changed)) break;
                     }
                 }
-
-                // --- choice with the reference's tie-break ---
-                int32_t right = __shfl_up_sync(0xffffffffu, cst, 1);
-                if (lane == 0) right = costRight;
-                int32_t t1 = __shfl_sync(0xffffffffu, cst, near1 ? (lane - (int)l1) : 0);
-                int32_t t2 = __shfl_sync(0xffffffffu, cst, near2 ? (lane - (int)l2) : 0);
-                int32_t c1 = near1 ? a1 + t1 : f1;
-                int32_t c2 = near2 ? a2 + t2 : f2;
-                int32_t best = 9 + right;
-                uint32_t bo = 0, bl = 1;
-                if (l1 >= 3 && c1 < best) { best = c1; bo = (uint32_t)ra.w; bl = l1; }
-                if (l2 >= 3 && c2 < best) { best = c2; bo = (uint32_t)rb.w; bl = l2; }
-                if (p == 0 || p >= n) { bo = 0; bl = 1; }  // forced literals: position 0 and the 8-byte tail
-
                 ring[p & (2 * PC - 1)] = cst;
-                if (p < N) {
-                    if (p <= n) cs[p] = cst;
-                    ch[p] = make_int2((int)bo, (int)bl);
-                }
+                if (p <= n) cs[p] = cst;
                 costRight = __shfl_sync(0xffffffffu, cst, 31);
                 __syncwarp();
             }
         }
         __syncthreads();
     }
+    if (warp != 0) finish_chunk(stA, stB, cs, N, n, 0, ch, tid - 32, PARSE_THREADS - 32);
 }
 
 // jump[p] = first position >= the end of p's PARSE_CHUNK that the chosen parse
@@ -206,7 +216,12 @@ __global__ void __launch_bounds__(256) k_jump(const uint32_t *__restrict__ blkN,
 
 int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
 {
-    k_parse<<<bd.B, PARSE_THREADS, 0, st>>>(ws.cand, ws.blkN, bd.logS, ws.cost, ws.choice);
+    static bool attrSet = false;
+    if (!attrSet) {
+        cudaFuncSetAttribute(k_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PARSE_SMEM);
+        attrSet = true;
+    }
+    k_parse<<<bd.B, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, ws.cost, ws.choice);
     k_jump<<<bd.B << (bd.logS - PARSE_CHUNK_LOG), 256, 0, st>>>(ws.blkN, ws.choice, bd.logS, ws.jump);
     lc.launches += 2;
     cudaError_t e = cudaGetLastError();
