@@ -25,57 +25,80 @@ namespace {
 // The literal chain inside the window is a prefix-min scan in (min,+).
 // ---------------------------------------------------------------------------
 constexpr int PC = 512;            // positions per staged chunk
-constexpr int PARSE_THREADS = 128; // 1 consumer warp + 3 helper warps
+constexpr int HELPERS = 128;       // threads per helper group (stagers, finishers)
+constexpr int PER = PC / HELPERS;  // positions per helper thread and chunk
+constexpr int PARSE_THREADS = 32 + 2 * HELPERS;  // consumer warp + stagers + finishers
 constexpr int NOT_FAR = -1;
 constexpr size_t PARSE_SMEM = 3 * PC * 2 * sizeof(int4) + 2 * PC * sizeof(int32_t);
 
 // record: x = len (>= 3), y = weight, z = weight + final target cost or NOT_FAR, w = offs.
-// An absent candidate is staged as far with cost INF.
+// An absent candidate is staged as far with cost INF.  `tid` in [0, HELPERS).
 __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const int32_t *cs, uint32_t n,
-                                            uint32_t chunk, int4 *sa, int4 *sb, int tid, int nthreads)
+                                            uint32_t chunk, int4 *sa, int4 *sb, int tid)
 {
     const uint32_t base = chunk * PC;
     const uint32_t farFrom = (chunk + 2) * PC;  // targets >= this are final and visible
-    for (uint32_t i = tid; i < PC; i += nthreads) {
-        const uint32_t p = base + i;
+    int4 c[PER];
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+        const uint32_t p = base + tid + k * HELPERS;
+        c[k] = (p >= 1 && p < n) ? cd[p] : make_int4(0, 0, 0, 0);
+    }
+    int32_t t1[PER], t2[PER];
+#pragma unroll
+    for (int k = 0; k < PER; k++) {  // all far-cost loads in flight together
+        const uint32_t p = base + tid + k * HELPERS;
+        const uint32_t ta = p + (uint32_t)c[k].y, tb = p + (uint32_t)c[k].w;
+        t1[k] = (c[k].y >= 3 && ta >= farFrom) ? __ldcg(&cs[ta]) : NOT_FAR;
+        t2[k] = (c[k].w >= 3 && tb >= farFrom) ? __ldcg(&cs[tb]) : NOT_FAR;
+    }
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
         int4 a = make_int4(0, 0, SALZ_INF, 0), b = make_int4(0, 0, SALZ_INF, 0);
-        if (p >= 1 && p < n) {
-            const int4 c = cd[p];
-            if (c.y >= 3) {
-                const int w = factor_cost_bits((uint32_t)c.x, (uint32_t)c.y);
-                const uint32_t t = p + (uint32_t)c.y;
-                a = make_int4(c.y, w, (t >= farFrom) ? w + __ldcg(&cs[t]) : NOT_FAR, c.x);
-            }
-            if (c.w >= 3) {
-                const int w = factor_cost_bits((uint32_t)c.z, (uint32_t)c.w);
-                const uint32_t t = p + (uint32_t)c.w;
-                b = make_int4(c.w, w, (t >= farFrom) ? w + __ldcg(&cs[t]) : NOT_FAR, c.z);
-            }
+        if (c[k].y >= 3) {
+            const int w = factor_cost_bits((uint32_t)c[k].x, (uint32_t)c[k].y);
+            a = make_int4(c[k].y, w, (t1[k] != NOT_FAR) ? w + t1[k] : NOT_FAR, c[k].x);
         }
-        sa[i] = a;
-        sb[i] = b;
+        if (c[k].w >= 3) {
+            const int w = factor_cost_bits((uint32_t)c[k].z, (uint32_t)c[k].w);
+            b = make_int4(c[k].w, w, (t2[k] != NOT_FAR) ? w + t2[k] : NOT_FAR, c[k].z);
+        }
+        sa[tid + k * HELPERS] = a;
+        sb[tid + k * HELPERS] = b;
     }
 }
 
 // Choices of a chunk whose costs (and every cost to its right) are final.
 __device__ __forceinline__ void finish_chunk(const int4 *sa, const int4 *sb, const int32_t *cs, uint32_t N, uint32_t n,
-                                             uint32_t chunk, int2 *__restrict__ ch, int tid, int nthreads)
+                                             uint32_t chunk, int2 *__restrict__ ch, int tid)
 {
     const uint32_t base = chunk * PC;
-    for (uint32_t i = tid; i < PC; i += nthreads) {
-        const uint32_t p = base + i;
+    int4 a[PER], b[PER];
+    int32_t r0[PER], r1[PER], r2[PER];
+#pragma unroll
+    for (int k = 0; k < PER; k++) {  // all cost loads in flight together
+        const uint32_t p = base + tid + k * HELPERS;
+        a[k] = sa[tid + k * HELPERS];
+        b[k] = sb[tid + k * HELPERS];
+        const bool in = p >= 1 && p < n;  // position 0 and the 8-byte tail are forced literals
+        r0[k] = in ? __ldcg(&cs[p + 1]) : 0;
+        r1[k] = (in && a[k].z == NOT_FAR) ? __ldcg(&cs[p + (uint32_t)a[k].x]) : 0;
+        r2[k] = (in && b[k].z == NOT_FAR) ? __ldcg(&cs[p + (uint32_t)b[k].x]) : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+        const uint32_t p = base + tid + k * HELPERS;
         if (p >= N) break;
         uint32_t bo = 0, bl = 1;
-        if (p >= 1 && p < n) {  // position 0 and the 8-byte tail are forced literals
-            const int4 a = sa[i], b = sb[i];
-            int32_t best = 9 + __ldcg(&cs[p + 1]);
-            if (a.z != SALZ_INF) {
-                const int32_t c1 = (a.z != NOT_FAR) ? a.z : a.y + __ldcg(&cs[p + (uint32_t)a.x]);
-                if (c1 < best) { best = c1; bo = (uint32_t)a.w; bl = (uint32_t)a.x; }
+        if (p >= 1 && p < n) {
+            int32_t best = 9 + r0[k];
+            if (a[k].z != SALZ_INF) {
+                const int32_t c1 = (a[k].z != NOT_FAR) ? a[k].z : a[k].y + r1[k];
+                if (c1 < best) { best = c1; bo = (uint32_t)a[k].w; bl = (uint32_t)a[k].x; }
             }
-            if (b.z != SALZ_INF) {
-                const int32_t c2 = (b.z != NOT_FAR) ? b.z : b.y + __ldcg(&cs[p + (uint32_t)b.x]);
-                if (c2 < best) { best = c2; bo = (uint32_t)b.w; bl = (uint32_t)b.x; }
+            if (b[k].z != SALZ_INF) {
+                const int32_t c2 = (b[k].z != NOT_FAR) ? b[k].z : b[k].y + r2[k];
+                if (c2 < best) { best = c2; bo = (uint32_t)b[k].w; bl = (uint32_t)b[k].x; }
             }
         }
         ch[p] = make_int2((int)bo, (int)bl);
@@ -100,21 +123,20 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
     int2 *ch = choice + gb;
 
     const uint32_t nChunks = (N + PC - 1) / PC;
-    {
+    if (warp >= 1 && warp <= HELPERS / 32) {
         const uint32_t c = nChunks - 1;
-        stage_chunk(cd, cs, n, c, stA + (c % 3) * PC, stB + (c % 3) * PC, tid, PARSE_THREADS);
+        stage_chunk(cd, cs, n, c, stA + (c % 3) * PC, stB + (c % 3) * PC, tid - 32);
     }
     __syncthreads();
 
     int32_t costRight = SALZ_INF;  // cost[q+1] of the window being processed
     for (uint32_t c = nChunks; c-- > 0;) {
-        if (warp != 0) {
+        if (warp > HELPERS / 32) {
             if (c + 1 < nChunks)
-                finish_chunk(stA + ((c + 1) % 3) * PC, stB + ((c + 1) % 3) * PC, cs, N, n, c + 1, ch, tid - 32,
-                             PARSE_THREADS - 32);
-            if (c > 0)
-                stage_chunk(cd, cs, n, c - 1, stA + ((c - 1) % 3) * PC, stB + ((c - 1) % 3) * PC, tid - 32,
-                            PARSE_THREADS - 32);
+                finish_chunk(stA + ((c + 1) % 3) * PC, stB + ((c + 1) % 3) * PC, cs, N, n, c + 1, ch,
+                             tid - 32 - HELPERS);
+        } else if (warp >= 1) {
+            if (c > 0) stage_chunk(cd, cs, n, c - 1, stA + ((c - 1) % 3) * PC, stB + ((c - 1) % 3) * PC, tid - 32);
         } else {
             const int4 *sa = stA + (c % 3) * PC, *sb = stB + (c % 3) * PC;
             const uint32_t lastP = min(N - 1, c * PC + PC - 1);
@@ -169,7 +191,7 @@ __global__ void __launch_bounds__(PARSE_THREADS) k_parse(const int4 *__restrict_
         }
         __syncthreads();
     }
-    if (warp != 0) finish_chunk(stA, stB, cs, N, n, 0, ch, tid - 32, PARSE_THREADS - 32);
+    if (warp > HELPERS / 32) finish_chunk(stA, stB, cs, N, n, 0, ch, tid - 32 - HELPERS);
 }
 
 // jump[p] = first position >= the end of p's PARSE_CHUNK that the chosen parse
