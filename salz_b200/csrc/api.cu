@@ -87,6 +87,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
 
     Workspace &ws = c->ws;
     memset(&ws, 0, sizeof(ws));
+    cudaDeviceGetAttribute(&ws.numSMs, cudaDevAttrMultiProcessorCount, device);
+    if (ws.numSMs <= 0) ws.numSMs = 148;
     int logS = 12;
     while (((size_t)1 << logS) < max_block_len) logS++;
     ws.logS = logS;
@@ -111,7 +113,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
         ok = ok && dalloc(c, &ws.listCnt[i], B) && dalloc(c, &ws.listBase[i], B + 1) && dalloc(c, &ws.tileBase[i], B + 1);
     }
     ws.tileCap = M / sa_tile_elems() + B + 2;
-    for (int i = 0; i < 2 && ok; i++) ok = dalloc(c, &ws.tileBlock[i], ws.tileCap);
+    for (int i = 0; i < 2 && ok; i++) ok = dalloc(c, &ws.tileDesc[i], ws.tileCap);
     ok = ok && dalloc(c, &ws.rank, M + 64) && dalloc(c, &ws.SA, M + 64);
     ok = ok && dalloc(c, &ws.hist, B * 8 * 256) && dalloc(c, &ws.digitBase, B * 8 * 256);
     ok = ok && dalloc(c, &ws.tileState, (ws.tileCap + 1) * 256);

@@ -25,6 +25,8 @@
 // Otherwise: u64 key (group | second) + u32 value p; 24 B per element.
 #include "salz_dev.cuh"
 
+#include <algorithm>
+
 namespace {
 
 #ifndef SALZ_TT
@@ -59,18 +61,19 @@ struct ListView {
     const uint32_t *cnt;        // [B]   elements of block b in the list
     const uint32_t *base;       // [B+1] list offset of block b
     const uint32_t *tileBase;   // [B+1] first tile of block b
-    const uint32_t *tileBlock;  // [tiles] block of tile t
+    const uint4 *tileDesc;      // [tiles] (block, tile index inside the block, first element, elements)
 };
 
 struct TileLoc { uint32_t b, lt, first, valid; };
 
 __device__ __forceinline__ TileLoc locate(const ListView &lv, uint32_t tile)
 {
+    const uint4 d = lv.tileDesc[tile];
     TileLoc t;
-    t.b = lv.tileBlock[tile];
-    t.lt = tile - lv.tileBase[t.b];
-    t.first = lv.base[t.b] + t.lt * TILE;
-    t.valid = min((uint32_t)TILE, lv.cnt[t.b] - t.lt * TILE);
+    t.b = d.x;
+    t.lt = d.y;
+    t.first = d.z;
+    t.valid = d.w;
     return t;
 }
 
@@ -149,11 +152,15 @@ __global__ void __launch_bounds__(1024) k_tilemap(const uint32_t *__restrict__ c
     }
 }
 
-__global__ void __launch_bounds__(128) k_tilefill(const uint32_t *__restrict__ tileBase, uint32_t *__restrict__ tileBlock)
+__global__ void __launch_bounds__(128) k_tilefill(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ base,
+                                                  const uint32_t *__restrict__ tileBase, uint4 *__restrict__ tileDesc)
 {
     const uint32_t b = blockIdx.x;
-    const uint32_t lo = tileBase[b], hi = tileBase[b + 1];
-    for (uint32_t t = lo + threadIdx.x; t < hi; t += blockDim.x) tileBlock[t] = b;
+    const uint32_t lo = tileBase[b], hi = tileBase[b + 1], c = cnt[b], first = base[b];
+    for (uint32_t t = lo + threadIdx.x; t < hi; t += blockDim.x) {
+        const uint32_t lt = t - lo;
+        tileDesc[t] = make_uint4(b, lt, first + lt * TILE, min((uint32_t)TILE, c - lt * TILE));
+    }
 }
 
 // ---- key construction -----------------------------------------------------------
@@ -257,114 +264,157 @@ constexpr int SCATTER_MIN_CTAS = (TT * ITEMS <= 2048) ? 4 : 2;
 template <bool PACKED, bool MATCH_ANY>
 __global__ void __launch_bounds__(TT, SCATTER_MIN_CTAS)
 k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn, uint64_t *__restrict__ keysOut,
-          uint32_t *__restrict__ valsOut, ListView lv, int shift, int pass, const uint32_t *__restrict__ digitBase,
-          uint32_t *tileState)
+          uint32_t *__restrict__ valsOut, ListView lv, uint32_t numTiles, int shift, int pass,
+          const uint32_t *__restrict__ digitBase, uint32_t *tileState)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     uint64_t *skeys = (uint64_t *)smem;                 // [TILE] keys in digit order
     uint32_t *wcnt = (uint32_t *)(skeys + TILE);        // [WARPS][256] per-warp digit counts -> running offsets
-    uint32_t *masks = wcnt + WARPS * 256;               // [WARPS][256] peer masks
+    uint32_t *masks = wcnt + WARPS * 256;               // [WARPS][256] peer masks (self-cleaning)
     uint32_t *dstart = masks + WARPS * 256;             // [256]
     uint32_t *gbase = dstart + 256;                     // [256]
     uint32_t *scratch = gbase + 256;                    // [16]
     uint32_t *svals = scratch + 16;                     // [TILE] (pairs only)
-    __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_tile[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(tileState, 1u);
-    for (int i = tid; i < 2 * WARPS * 256; i += TT) wcnt[i] = 0;  // counts and masks
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const TileLoc tl = locate(lv, tile);
     uint32_t *state = tileState + 256;
-
-    uint64_t key[ITEMS];
-    uint32_t val[ITEMS];
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
-        if (idx < tl.valid) {
-            key[i] = keysIn[tl.first + idx];
-            if (!PACKED) val[i] = valsIn[tl.first + idx];
-        } else {
-            key[i] = ~0ull;
-            if (!PACKED) val[i] = 0;
-        }
-    }
-    // early counts: the tile's digit histogram is published before the ranking so
-    // that successors find an inclusive prefix by the time they look back
     uint32_t *mycnt = wcnt + warp * 256;
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) atomicAdd(&mycnt[(uint32_t)(key[i] >> shift) & 255u], 1u);
-    __syncthreads();
-
-    uint32_t total = 0;
-    if (tid < 256) {
-        uint32_t sum = 0;
-#pragma unroll
-        for (int w = 0; w < WARPS; w++) {
-            uint32_t c = wcnt[w * 256 + tid];
-            wcnt[w * 256 + tid] = sum;
-            sum += c;
-        }
-        total = sum;
-        const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
-        st_relaxed(&state[(size_t)tile * 256 + tid], (tl.lt == 0 ? LB_INCL : LB_AGG) | cnt);
-    }
-    const uint32_t ex = excl_scan_first256(total, scratch);
-    if (tid < 256) dstart[tid] = ex;
-    __syncthreads();
-
-    // ranking: peers of a lane = lanes of the warp holding the same digit
     uint32_t *mymask = masks + warp * 256;
     const uint32_t lt_mask = (1u << lane) - 1u;
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-        uint32_t m;
-        if (MATCH_ANY) {
-            m = __match_any_sync(0xffffffffu, d);
-        } else {
-            atomicOr(&mymask[d], 1u << lane);
-            __syncwarp();
-            m = mymask[d];
-            __syncwarp();
-        }
-        const int leader = __ffs(m) - 1;
-        uint32_t pre = 0;
-        if (lane == leader) {
-            pre = mycnt[d];
-            mycnt[d] = pre + __popc(m);
-            if (!MATCH_ANY) mymask[d] = 0;
-        }
-        pre = __shfl_sync(0xffffffffu, pre, leader);
-        const uint32_t pos = dstart[d] + pre + __popc(m & lt_mask);
-        skeys[pos] = key[i];
-        if (!PACKED) svals[pos] = val[i];
-        __syncwarp();
-    }
 
-    if (tid < 256) {
-        uint32_t prev = 0;
-        if (tl.lt != 0) {
-            for (uint32_t t = tile - 1;; --t) {
-                uint32_t s;
-                do { s = ld_relaxed(&state[(size_t)t * 256 + tid]); } while ((s >> 30) == 0);
-                prev += s & LB_MASK;
-                if ((s >> 30) == 2) break;
-            }
-            const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
-            st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | (prev + cnt));
-        }
-        gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pass) * 256 + tid] + prev - ex;
-    }
+    // Persistent CTA: tiles are claimed by ticket (so every predecessor in a
+    // look-back chain is already running), and the next tile's descriptor and
+    // keys are fetched while the current tile is ranked and written.
+    if (tid == 0) s_tile[0] = atomicAdd(tileState, 1u);
+    for (int i = tid; i < WARPS * 256; i += TT) masks[i] = 0;
     __syncthreads();
+    uint32_t tile = s_tile[0];
+    int par = 0;
+    TileLoc nl = {0, 0, 0, 0};
+    uint64_t nkey[ITEMS];
+    uint32_t nval[ITEMS];
+    if (tile < numTiles) {
+        nl = locate(lv, tile);
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
+            nkey[i] = (idx < nl.valid) ? keysIn[nl.first + idx] : ~0ull;
+            if (!PACKED) nval[i] = (idx < nl.valid) ? valsIn[nl.first + idx] : 0u;
+        }
+    }
 
-    for (uint32_t j = tid; j < tl.valid; j += TT) {
-        const uint64_t k = skeys[j];
-        const uint32_t dst = gbase[(uint32_t)(k >> shift) & 255u] + j;
-        keysOut[dst] = k;
-        if (!PACKED) valsOut[dst] = svals[j];
+    while (tile < numTiles) {
+        const TileLoc tl = nl;
+        uint64_t key[ITEMS];
+        uint32_t val[ITEMS];
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            key[i] = nkey[i];
+            if (!PACKED) val[i] = nval[i];
+        }
+        for (int i = tid; i < WARPS * 256; i += TT) wcnt[i] = 0;
+        if (tid == 0) s_tile[par ^ 1] = atomicAdd(tileState, 1u);
+        __syncthreads();
+        const uint32_t nextTile = s_tile[par ^ 1];
+        uint4 nd = make_uint4(0, 0, 0, 0);
+        if (nextTile < numTiles) nd = lv.tileDesc[nextTile];
+
+        // early counts: the tile's digit histogram is published before the ranking so
+        // that successors find an inclusive prefix by the time they look back
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
+            // a warp-uniform digit (the rule in the passes over the group bits) would
+            // serialise 32 same-address atomics: one lane adds 32 instead
+            if (__all_sync(0xffffffffu, d == __shfl_sync(0xffffffffu, d, 0))) {
+                if (lane == 0) mycnt[d] += 32;
+            } else {
+                atomicAdd(&mycnt[d], 1u);
+            }
+        }
+        __syncthreads();
+
+        uint32_t total = 0;
+        if (tid < 256) {
+            uint32_t sum = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) {
+                uint32_t c = wcnt[w * 256 + tid];
+                wcnt[w * 256 + tid] = sum;
+                sum += c;
+            }
+            total = sum;
+            const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
+            st_relaxed(&state[(size_t)tile * 256 + tid], (tl.lt == 0 ? LB_INCL : LB_AGG) | cnt);
+        }
+        const uint32_t ex = excl_scan_first256(total, scratch);
+        if (tid < 256) dstart[tid] = ex;
+        __syncthreads();
+
+        // next tile's keys: in flight during ranking, look-back and write-out
+        nl.b = nd.x; nl.lt = nd.y; nl.first = nd.z; nl.valid = nd.w;
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
+            nkey[i] = (idx < nl.valid) ? keysIn[nl.first + idx] : ~0ull;
+            if (!PACKED) nval[i] = (idx < nl.valid) ? valsIn[nl.first + idx] : 0u;
+        }
+
+        // ranking: peers of a lane = lanes of the warp holding the same digit
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
+            uint32_t m;
+            const bool uniform = __all_sync(0xffffffffu, d == __shfl_sync(0xffffffffu, d, 0));
+            if (uniform) {
+                m = 0xffffffffu;
+            } else if (MATCH_ANY) {
+                m = __match_any_sync(0xffffffffu, d);
+            } else {
+                atomicOr(&mymask[d], 1u << lane);
+                __syncwarp();
+                m = mymask[d];
+                __syncwarp();
+            }
+            const int leader = __ffs(m) - 1;
+            uint32_t pre = 0;
+            if (lane == leader) {
+                pre = mycnt[d];
+                mycnt[d] = pre + __popc(m);
+                if (!MATCH_ANY && !uniform) mymask[d] = 0;
+            }
+            pre = __shfl_sync(0xffffffffu, pre, leader);
+            const uint32_t pos = dstart[d] + pre + __popc(m & lt_mask);
+            skeys[pos] = key[i];
+            if (!PACKED) svals[pos] = val[i];
+            __syncwarp();
+        }
+
+        if (tid < 256) {
+            uint32_t prev = 0;
+            if (tl.lt != 0) {
+                for (uint32_t t = tile - 1;; --t) {
+                    uint32_t s;
+                    do { s = ld_relaxed(&state[(size_t)t * 256 + tid]); } while ((s >> 30) == 0);
+                    prev += s & LB_MASK;
+                    if ((s >> 30) == 2) break;
+                }
+                const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
+                st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | (prev + cnt));
+            }
+            gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pass) * 256 + tid] + prev - ex;
+        }
+        __syncthreads();
+
+        for (uint32_t j = tid; j < tl.valid; j += TT) {
+            const uint64_t k = skeys[j];
+            const uint32_t dst = gbase[(uint32_t)(k >> shift) & 255u] + j;
+            keysOut[dst] = k;
+            if (!PACKED) valsOut[dst] = svals[j];
+        }
+        tile = nextTile;
+        par ^= 1;
     }
 }
 
@@ -625,7 +675,7 @@ ListView view(const Workspace &ws, int i)
     lv.cnt = ws.listCnt[i];
     lv.base = ws.listBase[i];
     lv.tileBase = ws.tileBase[i];
-    lv.tileBlock = ws.tileBlock[i];
+    lv.tileDesc = ws.tileDesc[i];
     return lv;
 }
 
@@ -634,16 +684,17 @@ int radix_sort(SortCtx &s, int passes, int shift0)
 {
     Workspace &ws = s.ws;
     const size_t smem = PACKED ? SCATTER_SMEM_PACKED : SCATTER_SMEM_PAIRS;
+    const uint32_t grid = std::min<uint32_t>(s.tiles, (uint32_t)(s.ws.numSMs * SCATTER_MIN_CTAS));
     for (int ps = 0; ps < passes; ps++) {
         CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)s.tiles + 1) * 256 * 4, s.st));
         if (s.matchAny)
-            k_scatter<PACKED, true><<<s.tiles, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
-                                                                 ws.vals[s.cur ^ 1], view(ws, s.lcur), shift0 + 8 * ps,
-                                                                 ps, ws.digitBase, ws.tileState);
+            k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
+                                                              ws.vals[s.cur ^ 1], view(ws, s.lcur), s.tiles,
+                                                              shift0 + 8 * ps, ps, ws.digitBase, ws.tileState);
         else
-            k_scatter<PACKED, false><<<s.tiles, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
-                                                                  ws.vals[s.cur ^ 1], view(ws, s.lcur), shift0 + 8 * ps,
-                                                                  ps, ws.digitBase, ws.tileState);
+            k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
+                                                               ws.vals[s.cur ^ 1], view(ws, s.lcur), s.tiles,
+                                                               shift0 + 8 * ps, ps, ws.digitBase, ws.tileState);
         s.lc.launches += 1;
         s.lc.sort_launches += 1;
         s.lc.sort_elems += s.count;
@@ -670,7 +721,7 @@ int rerank(SortCtx &s)
                                                              ws.aggPst, ws.aggKeep, ws.rank, ws.SA, ws.keys[s.cur ^ 1],
                                                              ws.vals[s.cur ^ 1], ws.listCnt[nxt]);
     k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[nxt], s.bd.B, ws.listBase[nxt], ws.tileBase[nxt], ws.counters);
-    k_tilefill<<<s.bd.B, 128, 0, s.st>>>(ws.tileBase[nxt], ws.tileBlock[nxt]);
+    k_tilefill<<<s.bd.B, 128, 0, s.st>>>(ws.listCnt[nxt], ws.listBase[nxt], ws.tileBase[nxt], ws.tileDesc[nxt]);
     s.lc.launches += 5;
     CK(cudaMemcpyAsync(ws.h_counters, ws.counters, 8, cudaMemcpyDeviceToHost, s.st));
     CK(cudaStreamSynchronize(s.st));
@@ -705,7 +756,7 @@ int sa_build_t(SortCtx &s, uint64_t &algBytes, int &rounds, float *msSort, cudaE
     // round 0
     k_first_counts<<<(bd.B + 255) / 256, 256, 0, s.st>>>(ws.blkN, bd.B, ws.listCnt[0]);
     k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[0], bd.B, ws.listBase[0], ws.tileBase[0], ws.counters);
-    k_tilefill<<<bd.B, 128, 0, s.st>>>(ws.tileBase[0], ws.tileBlock[0]);
+    k_tilefill<<<bd.B, 128, 0, s.st>>>(ws.listCnt[0], ws.listBase[0], ws.tileBase[0], ws.tileDesc[0]);
     CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
     k_init<PACKED><<<s.tiles, TT, 0, s.st>>>(ws.T, bd.Tstride, ws.blkN, view(ws, 0), logS, nchars, ws.keys[0], ws.vals[0],
                                              ws.hist);

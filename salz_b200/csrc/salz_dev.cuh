@@ -23,6 +23,7 @@ struct BatchDesc {
 };
 
 struct Workspace {
+    int numSMs;
     // capacity
     size_t Bmax;
     uint32_t S;
@@ -41,7 +42,7 @@ struct Workspace {
     uint32_t *listCnt[2];   // [Bmax]   list elements per block
     uint32_t *listBase[2];  // [Bmax+1] list offset per block
     uint32_t *tileBase[2];  // [Bmax+1] first tile per block
-    uint32_t *tileBlock[2]; // [tileCap] block of every tile
+    uint4 *tileDesc[2];     // [tileCap] (block, tile in block, first element, elements) of every tile
     size_t tileCap;
     uint32_t *hist;      // [Bmax][8][256] digit histograms for the coming sort
     uint32_t *digitBase; // [Bmax][8][256] exclusive scans of hist
