@@ -48,11 +48,13 @@ __device__ __forceinline__ uint64_t far_item(uint32_t slot, uint32_t right, int3
 __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ SA, const int32_t *__restrict__ LCP,
                                                   const uint32_t *__restrict__ blkN, int logS,
                                                   int2 *__restrict__ cand2, uint64_t *__restrict__ farItems,
-                                                  uint32_t *__restrict__ farCount)
+                                                  uint32_t *__restrict__ farCount, int32_t *__restrict__ tileMinV,
+                                                  int32_t *__restrict__ tileMinL)
 {
     __shared__ uint32_t sv[AT * APAD];   // (value << 8) | link
     __shared__ int32_t sm[AT * APAD];    // LCP, then the element's running minimum
     __shared__ int32_t segMin[AT], segLcp[AT];
+    __shared__ int32_t preV[AT], preL[AT], sufV[AT], sufL[AT];  // minima over the segments before / after
     __shared__ uint8_t segLen[AT];
 
     const int tid = threadIdx.x;
@@ -60,7 +62,10 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     const uint32_t b = blockIdx.x / tilesPerBlock, tb = blockIdx.x % tilesPerBlock;
     const uint32_t n = blkN[b] - 8;
     const uint32_t t0 = tb * ATS;  // first slot of the tile (local)
-    if (t0 >= n) return;
+    if (t0 >= n) {
+        if (tid == 0) { tileMinV[blockIdx.x] = AINF; tileMinL[blockIdx.x] = AINF; }
+        return;
+    }
     const size_t gb = (size_t)b << logS;
     int2 *cd = cand2 + 2 * gb;
 
@@ -108,6 +113,38 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         segLcp[tid] = lmin;
     }
     __syncthreads();
+    // exclusive prefix / suffix minima over the tile's segments: an element smaller
+    // than everything on one side skips the search (monotone SA: every element)
+    if (tid < 32) {
+        int32_t v[4], l[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) { v[k] = segMin[tid * 4 + k]; l[k] = segLcp[tid * 4 + k]; }
+        int32_t av = min(min(v[0], v[1]), min(v[2], v[3])), al = min(min(l[0], l[1]), min(l[2], l[3]));
+        int32_t pv = av, pl = al, sv_ = av, sl = al;  // inclusive scans over lanes
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int32_t a = __shfl_up_sync(0xffffffffu, pv, o), b2 = __shfl_up_sync(0xffffffffu, pl, o);
+            int32_t c = __shfl_down_sync(0xffffffffu, sv_, o), d = __shfl_down_sync(0xffffffffu, sl, o);
+            if (tid >= o) { pv = min(pv, a); pl = min(pl, b2); }
+            if (tid + o < 32) { sv_ = min(sv_, c); sl = min(sl, d); }
+        }
+        if (tid == 31) { tileMinV[blockIdx.x] = pv; tileMinL[blockIdx.x] = pl; }
+        int32_t ev = __shfl_up_sync(0xffffffffu, pv, 1), el = __shfl_up_sync(0xffffffffu, pl, 1);
+        if (tid == 0) { ev = AINF; el = AINF; }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            preV[tid * 4 + k] = ev; preL[tid * 4 + k] = el;
+            ev = min(ev, v[k]); el = min(el, l[k]);
+        }
+        ev = __shfl_down_sync(0xffffffffu, sv_, 1); el = __shfl_down_sync(0xffffffffu, sl, 1);
+        if (tid == 31) { ev = AINF; el = AINF; }
+#pragma unroll
+        for (int k = 3; k >= 0; k--) {
+            sufV[tid * 4 + k] = ev; sufL[tid * 4 + k] = el;
+            ev = min(ev, v[k]); el = min(el, l[k]);
+        }
+    }
+    __syncthreads();
     if (len == 0) return;
 
     const bool firstTile = (tb == 0), lastTile = (t0 + ATS >= n);
@@ -117,9 +154,14 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         const int32_t v = (int32_t)(w >> 8);
         int32_t acc = sm[sb + i];
         int s = tid - 1;
-        for (; s >= 0; s--) {
-            if (segMin[s] < v) break;
-            acc = min(acc, segLcp[s]);
+        if (v < preV[tid]) {
+            acc = min(acc, preL[tid]);
+            s = -1;
+        } else {
+            for (; s >= 0; s--) {
+                if (segMin[s] < v) break;
+                acc = min(acc, segLcp[s]);
+            }
         }
         if (s >= 0) {
             int e = s * APAD + segLen[s] - 1;      // top of that segment's final stack
@@ -144,9 +186,14 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
             const int32_t v = (int32_t)(w >> 8);
             int32_t acc = accR;
             int s = tid + 1;
-            for (; s < AT; s++) {
-                if (segMin[s] < v) break;
-                acc = min(acc, segLcp[s]);
+            if (v < sufV[tid]) {
+                acc = min(acc, sufL[tid]);
+                s = AT;
+            } else {
+                for (; s < AT; s++) {
+                    if (segMin[s] < v) break;
+                    acc = min(acc, segLcp[s]);
+                }
             }
             if (s < AT) {
                 int f = s * APAD;                  // first prefix minimum of that segment
@@ -169,7 +216,8 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_ansv_far(Pyr py, const uint32_t *__restrict__ blkN,
                                                   const uint64_t *__restrict__ farItems,
-                                                  const uint32_t *__restrict__ farCount, int2 *__restrict__ cand2)
+                                                  const uint32_t *__restrict__ farCount, int2 *__restrict__ cand2,
+                                                  const int32_t *__restrict__ tpreV, const int32_t *__restrict__ tsufV)
 {
     const int logS = py.logS;
     const uint32_t Smask = (1u << logS) - 1;
@@ -195,7 +243,12 @@ __global__ void __launch_bounds__(256) k_ansv_far(Pyr py, const uint32_t *__rest
         int fl = -1;
         uint32_t fj = 0;
         int2 o = make_int2(v + 1, 0);  // none found
-        if (!right) {
+        const uint32_t tileG = slot / ATS;
+        if (!right && v < tpreV[tileG]) {
+            cand2[2 * (((size_t)b << logS) + (uint32_t)v)] = o;      // smaller than every slot before the tile
+        } else if (right && v < tsufV[tileG]) {
+            cand2[2 * (((size_t)b << logS) + (uint32_t)v) + 1] = o;  // smaller than every slot after the tile
+        } else if (!right) {
             // scan slots < tile start; m already covers (tile start - 1, r]
             int lvl = 0;
             uint32_t pos = r & ~(uint32_t)(ATS - 1);
@@ -252,6 +305,20 @@ __global__ void __launch_bounds__(256) k_ansv_far(Pyr py, const uint32_t *__rest
     }
 }
 
+// Per block: exclusive prefix / suffix minima of the tile minima (values only).
+__global__ void __launch_bounds__(32) k_ansv_tilescan(const int32_t *__restrict__ tileMinV, uint32_t tilesPerBlock,
+                                                      int32_t *__restrict__ tpreV, int32_t *__restrict__ tsufV)
+{
+    const size_t o = (size_t)blockIdx.x * tilesPerBlock;
+    if (threadIdx.x == 0) {
+        int32_t m = AINF;
+        for (uint32_t t = 0; t < tilesPerBlock; t++) { tpreV[o + t] = m; m = min(m, tileMinV[o + t]); }
+    } else if (threadIdx.x == 1) {
+        int32_t m = AINF;
+        for (uint32_t t = tilesPerBlock; t-- > 0;) { tsufV[o + t] = m; m = min(m, tileMinV[o + t]); }
+    }
+}
+
 // position 0 is a forced literal (ref lib/salz.c:546-548)
 __global__ void k_cand0(int4 *__restrict__ cand, int logS, int B)
 {
@@ -279,10 +346,11 @@ int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounte
     uint64_t *farItems = ws.keys[0];  // the sort buffers are free once the suffix array is complete
     cudaMemsetAsync(farCount, 0, 4, st);
     k_ansv_tile<<<(uint32_t)(total / ATS), AT, 0, st>>>(ws.SA, ws.lcp, ws.blkN, bd.logS, (int2 *)ws.cand, farItems,
-                                                        farCount);
-    k_ansv_far<<<148 * 8, 256, 0, st>>>(py, ws.blkN, farItems, farCount, (int2 *)ws.cand);
+                                                        farCount, ws.tileMinV, ws.tileMinL);
+    k_ansv_tilescan<<<bd.B, 32, 0, st>>>(ws.tileMinV, bd.S / ATS, ws.tilePreV, ws.tileSufV);
+    k_ansv_far<<<148 * 8, 256, 0, st>>>(py, ws.blkN, farItems, farCount, (int2 *)ws.cand, ws.tilePreV, ws.tileSufV);
     k_cand0<<<(bd.B + 127) / 128, 128, 0, st>>>(ws.cand, bd.logS, bd.B);
-    lc.launches += 3;
+    lc.launches += 4;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "salz_cuda: ansv_build: %s\n", cudaGetErrorString(e));

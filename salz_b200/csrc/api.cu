@@ -124,6 +124,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
         size_t cnt = (5 * l <= logS) ? (M >> (5 * l)) : 0;
         ok = dalloc(c, &ws.pyrSA[l], cnt + 32) && dalloc(c, &ws.pyrLCP[l], cnt + 32);
     }
+    ok = ok && dalloc(c, &ws.tileMinV, M / 4096 + 1) && dalloc(c, &ws.tileMinL, M / 4096 + 1) &&
+         dalloc(c, &ws.tilePreV, M / 4096 + 1) && dalloc(c, &ws.tileSufV, M / 4096 + 1);
     ok = ok && dalloc(c, &ws.cand, M) && dalloc(c, &ws.cost, M + B + 64) && dalloc(c, &ws.choice, M);
     ok = ok && dalloc(c, &ws.jump, M);
     const size_t chunks = M >> PARSE_CHUNK_LOG;

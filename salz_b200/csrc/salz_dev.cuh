@@ -64,6 +64,8 @@ struct Workspace {
     int32_t *pyrLCP[6];
     int nlevels;       // number of levels including level 0
 
+    // ANSV tile summaries, [Mcap / 4096] each
+    int32_t *tileMinV, *tileMinL, *tilePreV, *tileSufV;
     // candidates / parse
     int4 *cand;        // [Mcap] by g
     int32_t *cost;     // [Mcap + Bmax... ] by g, n_b entry = 0  (size Mcap + 64)
