@@ -245,3 +245,20 @@ def test_cli_compress_matches_reference_cli(tmp_path):
     c = tmp_path / "c.bin"
     c.write_bytes(bytes(1 << 15))
     assert subprocess.run([os.path.join(ROOT, "programs", "salz"), "-k", "-q", "-0", str(c)]).returncode != 0
+
+
+def test_reference_cli_linked_against_this_library(tmp_path):
+    """Link-level drop-in: the unmodified reference CLI, linked to
+    lib/libsalz.so, writes the same file as the reference CLI with its own encoder."""
+    dropin = os.path.join(ROOT, "oracle", "_ref", "salz_ref_dropin")
+    ref_cli = os.path.join(ROOT, "oracle", "_ref", "salz_ref")
+    if not (os.path.exists(dropin) and os.path.exists(ref_cli)):
+        pytest.skip("prebuilt reference CLIs absent")
+    _host_lib()
+    data = np.concatenate([synth.english_like(3 * (1 << 17) + 5000, seed=6), synth.uniform_random(1 << 17, seed=7),
+                           np.full(70000, 65, np.uint8)])
+    a = tmp_path / "a.bin"; b = tmp_path / "b.bin"
+    a.write_bytes(data.tobytes()); b.write_bytes(data.tobytes())
+    subprocess.run([dropin, "-k", "-q", "-2", str(a)], check=True)
+    subprocess.run([ref_cli, "-k", "-q", "-2", str(b)], check=True)
+    assert (tmp_path / "a.bin.salz").read_bytes() == (tmp_path / "b.bin.salz").read_bytes()
