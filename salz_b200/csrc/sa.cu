@@ -40,6 +40,7 @@ constexpr int ITEMS = SALZ_ITEMS;
 constexpr int TILE = TT * ITEMS;    // elements per tile
 constexpr int WARPS = TT / 32;
 constexpr int MAXP = 8;             // radix passes per sort, at most
+constexpr int LBW = 8;              // look-back window (predecessor tiles fetched per round trip)
 
 constexpr uint32_t LB_AGG = 1u << 30;   // tile aggregate published
 constexpr uint32_t LB_INCL = 2u << 30;  // inclusive prefix published
@@ -394,11 +395,24 @@ k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ vals
         if (tid < 256) {
             uint32_t prev = 0;
             if (tl.lt != 0) {
-                for (uint32_t t = tile - 1;; --t) {
-                    uint32_t s;
-                    do { s = ld_relaxed(&state[(size_t)t * 256 + tid]); } while ((s >> 30) == 0);
-                    prev += s & LB_MASK;
-                    if ((s >> 30) == 2) break;
+                // windowed look-back: LBW predecessors are fetched at once so that a
+                // chain of aggregates costs one L2 round trip, not one per hop
+                uint32_t t = tile - 1;
+                for (bool done = false; !done;) {
+                    const uint32_t w = min((uint32_t)LBW, tl.lt - (tile - 1 - t));  // stay inside the block
+                    uint32_t sv[LBW];
+#pragma unroll
+                    for (int k = 0; k < LBW; k++)
+                        sv[k] = ((uint32_t)k < w) ? ld_relaxed(&state[(size_t)(t - k) * 256 + tid]) : 0u;
+#pragma unroll
+                    for (int k = 0; k < LBW; k++) {
+                        if (done || (uint32_t)k >= w) break;
+                        const uint32_t f = sv[k] >> 30;
+                        if (f == 0) break;             // not published yet: poll again from here
+                        prev += sv[k] & LB_MASK;
+                        t--;
+                        if (f == 2) done = true;
+                    }
                 }
                 const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
                 st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | (prev + cnt));
