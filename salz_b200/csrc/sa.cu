@@ -40,7 +40,10 @@ constexpr int ITEMS = SALZ_ITEMS;
 constexpr int TILE = TT * ITEMS;    // elements per tile
 constexpr int WARPS = TT / 32;
 constexpr int MAXP = 8;             // radix passes per sort, at most
-constexpr int LBW = 8;              // look-back window (predecessor tiles fetched per round trip)
+#ifndef SALZ_LBW
+#define SALZ_LBW 8
+#endif
+constexpr int LBW = SALZ_LBW;            // look-back window (predecessor tiles fetched per round trip)
 
 constexpr uint32_t LB_AGG = 1u << 30;   // tile aggregate published
 constexpr uint32_t LB_INCL = 2u << 30;  // inclusive prefix published
