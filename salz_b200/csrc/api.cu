@@ -108,13 +108,15 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ok = ok && dalloc(c, &ws.T, ws.Tcap);
     ok = ok && dalloc(c, &ws.blkN, B);
     const bool packed = 3 * logS <= 64;
-    for (int i = 0; i < 2 && ok; i++) {
+    for (int i = 0; i < 2 && ok; i++)
         ok = dalloc(c, &ws.keys[i], M + M / 4096 + 64) && dalloc(c, &ws.vals[i], packed ? 1 : M);  // keys[0] doubles as the ANSV far list
-        ok = ok && dalloc(c, &ws.listCnt[i], B) && dalloc(c, &ws.listBase[i], B + 1) && dalloc(c, &ws.tileBase[i], B + 1);
-    }
+    for (int i = 0; i < 3 && ok; i++)
+        ok = dalloc(c, &ws.listCnt[i], B) && dalloc(c, &ws.listBase[i], B + 1) && dalloc(c, &ws.tileBase[i], B + 1);
     ws.tileCap = M / sa_tile_elems() + B + 2;
-    for (int i = 0; i < 2 && ok; i++) ok = dalloc(c, &ws.tileDesc[i], ws.tileCap);
+    for (int i = 0; i < 3 && ok; i++) ok = dalloc(c, &ws.tileDesc[i], ws.tileCap);
     ok = ok && dalloc(c, &ws.rank, M + 64) && dalloc(c, &ws.SA, M + 64);
+    ok = ok && dalloc(c, &ws.cntSnap, B) && dalloc(c, &ws.alphaMask, B * 8) && dalloc(c, &ws.codeTab, B * 256) &&
+         dalloc(c, &ws.symBits, B) && dalloc(c, &ws.h0, B);
     ok = ok && dalloc(c, &ws.hist, B * 8 * 256) && dalloc(c, &ws.digitBase, B * 8 * 256);
     ok = ok && dalloc(c, &ws.tileState, (ws.tileCap + 1) * 256);
     ok = ok && dalloc(c, &ws.aggHead, ws.tileCap) && dalloc(c, &ws.aggPst, ws.tileCap) && dalloc(c, &ws.aggKeep, ws.tileCap);
@@ -126,7 +128,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     }
     ok = ok && dalloc(c, &ws.tileMinV, M / 4096 + 1) && dalloc(c, &ws.tileMinL, M / 4096 + 1) &&
          dalloc(c, &ws.tilePreV, M / 4096 + 1) && dalloc(c, &ws.tileSufV, M / 4096 + 1);
-    ok = ok && dalloc(c, &ws.cand, M) && dalloc(c, &ws.cost, M + B + 64) && dalloc(c, &ws.choice, M);
+    ok = ok && dalloc(c, &ws.cand, M + 64) && dalloc(c, &ws.cost, M + B + 64) && dalloc(c, &ws.choice, M);
+    ws.keys[2] = (uint64_t *)ws.cand;  // the candidates are written after the suffix array is complete
     ok = ok && dalloc(c, &ws.jump, M);
     const size_t chunks = M >> PARSE_CHUNK_LOG;
     ok = ok && dalloc(c, &ws.chunkEntry, chunks) && dalloc(c, &ws.chunkTok, chunks) &&

@@ -38,7 +38,7 @@ __device__ __forceinline__ uint32_t lcp_private(const uint8_t *Ta, const uint8_t
 
 __global__ void __launch_bounds__(LT) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
                                                          const uint32_t *__restrict__ blkN,
-                                                         const uint32_t *__restrict__ rank,
+                                                         const uint64_t *__restrict__ rank,
                                                          const uint32_t *__restrict__ SA, int logS,
                                                          int32_t *__restrict__ V, int32_t *__restrict__ tileMax)
 {
@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(LT) k_plcp_irreducible(const uint8_t *__restri
     uint32_t q = 0, cap = 0, l = 0;
     bool pending = false;
     if (p < n) {
-        uint32_t r = rank[g];
+        uint32_t r = (g & ~Smask) | ((uint32_t)rank[g] & 0xffffffu);  // padded global slot
         if ((r & Smask) == 0) {
             v = (int32_t)p;  // smallest suffix of the block: PLCP = 0
         } else {
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(256) k_plcp_scan_tiles(int32_t *__restrict__ t
 
 // PLCP[g] = inclusive-max(V)[g] - p, also scattered to LCP[ISA[g]].
 __global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ blkN,
-                                                   const uint32_t *__restrict__ rank, int logS,
+                                                   const uint64_t *__restrict__ rank, int logS,
                                                    const int32_t *__restrict__ tileMax, int32_t *__restrict__ V,
                                                    int32_t *__restrict__ lcp)
 {
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ 
     if (p < n) {
         int32_t pl = v - (int32_t)p;
         V[g] = pl;
-        lcp[rank[g]] = pl;
+        lcp[(g & ~Smask) | ((uint32_t)rank[g] & 0xffffffu)] = pl;
     }
 }
 

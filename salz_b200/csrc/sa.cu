@@ -23,6 +23,24 @@
 // Element formats.  PACKED (block capacity S <= 2^21): one u64 per element,
 //   (group:logS | second:logS | p:logS); a pass moves 16 B per element.
 // Otherwise: u64 key (group | second) + u32 value p; 24 B per element.
+//
+// PACKED batches take a cheaper route in the doubling rounds (k_local): the
+// list is a bag of contiguous groups, and a group that lies inside one
+// 4096-element window is sorted by its second key in shared memory (register
+// sorting network + merge-path merges that skip already ordered runs),
+// re-ranked and compacted by the same CTA - one read and one write of the
+// element instead of five scatter passes.  Only groups that cross a window
+// boundary (large groups, and the odd unlucky small one) are forwarded to the
+// global radix path above; their survivors are appended to the bag again.
+//
+// Round 0 sorts by the first h0 characters after remapping the block's bytes to
+// dense codes of ceil(log2(sigma)) bits (k_alphabet), so 2 logS key bits cover
+// 8 characters of 30-symbol text or 20 characters of DNA instead of 5 bytes.
+//
+// rank entries are u64 (stamp:8 | old:24 | new:24): a writer of round r keeps
+// the previous group id in `old`, and a reader of round r that meets stamp r
+// uses `old` - all keys of a round are built from the same refinement even
+// though k_local reads and writes ranks in one launch.
 #include "salz_dev.cuh"
 
 #include <algorithm>
@@ -44,6 +62,25 @@ constexpr int MAXP = 8;             // radix passes per sort, at most
 #define SALZ_LBW 8
 #endif
 constexpr int LBW = SALZ_LBW;            // look-back window (predecessor tiles fetched per round trip)
+#ifndef SALZ_LT
+#define SALZ_LT 256
+#endif
+#ifndef SALZ_LITEMS
+#define SALZ_LITEMS 16
+#endif
+constexpr int LT = SALZ_LT;              // threads of a k_local CTA (power of two)
+constexpr int LITEMS = SALZ_LITEMS;      // elements per thread
+constexpr int LTILE = LT * LITEMS;       // window of the local path
+constexpr int NCH_MAX = 40;              // characters in a round-0 key, at most
+
+__device__ __forceinline__ uint32_t rk_read(uint64_t v, uint32_t round)
+{
+    return ((uint32_t)(v >> 56) == round) ? ((uint32_t)(v >> 24) & 0xffffffu) : ((uint32_t)v & 0xffffffu);
+}
+__device__ __forceinline__ uint64_t rk_make(uint32_t round, uint32_t old, uint32_t nw)
+{
+    return ((uint64_t)round << 56) | ((uint64_t)old << 24) | nw;
+}
 
 constexpr uint32_t LB_AGG = 1u << 30;   // tile aggregate published
 constexpr uint32_t LB_INCL = 2u << 30;  // inclusive prefix published
@@ -113,10 +150,11 @@ __global__ void k_first_counts(const uint32_t *__restrict__ blkN, int B, uint32_
     if (b < B) cnt[b] = blkN[b] - 8;
 }
 
-// Single CTA: base / tileBase = exclusive prefixes of cnt / tiles(cnt);
-// counters[0] = list length, counters[1] = tiles.
-__global__ void __launch_bounds__(1024) k_tilemap(const uint32_t *__restrict__ cnt, int B, uint32_t *__restrict__ base,
-                                                  uint32_t *__restrict__ tileBase, uint32_t *__restrict__ counters)
+// Single CTA: tileBase = exclusive prefix of tiles(cnt); every block's segment
+// starts at its padded offset b << logS; counters[0] = list length, [1] = tiles.
+__global__ void __launch_bounds__(1024) k_tilemap(const uint32_t *__restrict__ cnt, int B, uint32_t TILE, int logS,
+                                                  uint32_t *__restrict__ base, uint32_t *__restrict__ tileBase,
+                                                  uint32_t *__restrict__ counters)
 {
     __shared__ uint32_t pc[1024], pt[1024];
     const int tid = threadIdx.x;
@@ -142,14 +180,14 @@ __global__ void __launch_bounds__(1024) k_tilemap(const uint32_t *__restrict__ c
             pc[tid * 32 + i] = ra; pt[tid * 32 + i] = rt;
             ra += x; rt += y;
         }
-        if (tid == 31) { counters[0] = ia; counters[1] = it; base[B] = ia; tileBase[B] = it; }
+        if (tid == 31) { counters[0] = ia; counters[1] = it; base[B] = (uint32_t)B << logS; tileBase[B] = it; }
     }
     __syncthreads();
     sc = pc[tid];
     stl = pt[tid];
     for (int b = lo; b < hi; b++) {
         uint32_t c = cnt[b];
-        base[b] = sc;
+        base[b] = (uint32_t)b << logS;
         tileBase[b] = stl;
         sc += c;
         stl += (c + TILE - 1) / TILE;
@@ -157,13 +195,14 @@ __global__ void __launch_bounds__(1024) k_tilemap(const uint32_t *__restrict__ c
 }
 
 __global__ void __launch_bounds__(128) k_tilefill(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ base,
-                                                  const uint32_t *__restrict__ tileBase, uint4 *__restrict__ tileDesc)
+                                                  const uint32_t *__restrict__ tileBase, uint32_t TILE,
+                                                  uint4 *__restrict__ tileDesc)
 {
     const uint32_t b = blockIdx.x;
     const uint32_t lo = tileBase[b], hi = tileBase[b + 1], c = cnt[b], first = base[b];
     for (uint32_t t = lo + threadIdx.x; t < hi; t += blockDim.x) {
         const uint32_t lt = t - lo;
-        tileDesc[t] = make_uint4(b, lt, first + lt * TILE, min((uint32_t)TILE, c - lt * TILE));
+        tileDesc[t] = make_uint4(b, lt, first + lt * TILE, min(TILE, c - lt * TILE));
     }
 }
 
@@ -175,52 +214,130 @@ __device__ __forceinline__ void hist_flush(const uint32_t *sh, int passes, uint3
         if (sh[i]) atomicAdd(&hist[(size_t)b * MAXP * 256 + i], sh[i]);
 }
 
-// Round 0: key field = first `nchars` bytes of the suffix, big-endian, zero padded
-// past n_b.  Elements of a block are emitted in DESCENDING text position so that
-// the stable sort leaves zero-padded ties (only the last < nchars suffixes of a
-// block can be involved) in their correct order: shorter suffix first.
+// Byte values present in every block: mask[b] = 256-bit set.  grid = (chunks, B)
+constexpr int ALPHA_CHUNK = 1 << 16;
+__global__ void __launch_bounds__(256) k_alphabet(const uint8_t *__restrict__ T, size_t Tstride,
+                                                  const uint32_t *__restrict__ blkN, uint32_t *__restrict__ mask)
+{
+    __shared__ uint32_t sm[8];
+    const uint32_t b = blockIdx.y;
+    const uint32_t n = blkN[b] - 8;
+    const uint32_t lo = blockIdx.x * ALPHA_CHUNK;
+    if (lo >= n) return;
+    if (threadIdx.x < 8) sm[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t hi = min(n, lo + ALPHA_CHUNK);
+    const uint8_t *Tb = T + (size_t)b * Tstride;  // block starts are 16-byte aligned when Tstride is; fall back to bytes otherwise
+    const bool aligned = (((uintptr_t)Tb) & 15) == 0;
+    if (aligned) {
+        const uint4 *v = (const uint4 *)(Tb + lo);
+        const uint32_t words = (hi - lo) / 16;
+        for (uint32_t i = threadIdx.x; i < words; i += 256) {
+            const uint4 x = __ldg(v + i);
+            const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t c = (w[k] >> (8 * j)) & 255u;
+                    if (!((sm[c >> 5] >> (c & 31)) & 1u)) atomicOr(&sm[c >> 5], 1u << (c & 31));
+                }
+            }
+        }
+        for (uint32_t i = lo + words * 16 + threadIdx.x; i < hi; i += 256) {
+            const uint32_t c = Tb[i];
+            atomicOr(&sm[c >> 5], 1u << (c & 31));
+        }
+    } else {
+        for (uint32_t i = lo + threadIdx.x; i < hi; i += 256) {
+            const uint32_t c = Tb[i];
+            if (!((sm[c >> 5] >> (c & 31)) & 1u)) atomicOr(&sm[c >> 5], 1u << (c & 31));
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 8 && sm[threadIdx.x]) atomicOr(&mask[b * 8 + threadIdx.x], sm[threadIdx.x]);
+}
+
+// Dense order-preserving codes (from 1) of the bytes of block b, bits per code, and the
+// number of characters h0[b] a round-0 key of `fieldBits` bits holds.  grid = B
+__global__ void __launch_bounds__(256) k_alpha_finish(const uint32_t *__restrict__ mask, int fieldBits,
+                                                      uint16_t *__restrict__ codeTab, uint32_t *__restrict__ symBits,
+                                                      uint32_t *__restrict__ h0)
+{
+    __shared__ uint32_t sm[8];
+    const uint32_t b = blockIdx.x, c = threadIdx.x;
+    if (c < 8) sm[c] = mask[b * 8 + c];
+    __syncthreads();
+    uint32_t below = 0, sigma = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const uint32_t m = sm[w];
+        sigma += __popc(m);
+        if ((uint32_t)w < (c >> 5)) below += __popc(m);
+        else if ((uint32_t)w == (c >> 5)) below += __popc(m & ((1u << (c & 31)) - 1u));
+    }
+    const bool present = (sm[c >> 5] >> (c & 31)) & 1u;
+    codeTab[b * 256 + c] = present ? (uint16_t)(below + 1) : 0;  // 0 is the padding past the end, and nothing else
+    if (c == 0) {
+        const uint32_t bits = 32u - __clz(sigma);  // codes 1..sigma
+        symBits[b] = bits;
+        h0[b] = min((uint32_t)NCH_MAX, (uint32_t)fieldBits / bits);
+    }
+}
+
+// Round 0: key field = codes of the first h0[b] characters of the suffix, most
+// significant first, zero padded past n_b.  Codes start at 1, so equal keys mean
+// equal characters AND equal length inside the window: a suffix that ends within
+// the compared prefix is alone in its group, here and in every later round
+// (nothing relies on the stability of the sort across rounds).
 template <bool PACKED>
 __global__ void __launch_bounds__(TT) k_init(const uint8_t *__restrict__ T, size_t Tstride,
-                                             const uint32_t *__restrict__ blkN, ListView lv, int logS, int nchars,
-                                             uint64_t *__restrict__ keys, uint32_t *__restrict__ vals,
-                                             uint32_t *__restrict__ hist)
+                                             const uint32_t *__restrict__ blkN, ListView lv, int logS, int passes,
+                                             const uint16_t *__restrict__ codeTab, const uint32_t *__restrict__ symBits,
+                                             const uint32_t *__restrict__ h0, uint64_t *__restrict__ keys,
+                                             uint32_t *__restrict__ vals, uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t sh[MAXP * 256];
-    for (int i = threadIdx.x; i < nchars * 256; i += TT) sh[i] = 0;
-    __syncthreads();
+    __shared__ uint16_t scode[256];
+    __shared__ uint16_t stext[TILE + NCH_MAX + 8];
     const TileLoc tl = locate(lv, blockIdx.x);
+    for (int i = threadIdx.x; i < passes * 256; i += TT) sh[i] = 0;
+    if (threadIdx.x < 256) scode[threadIdx.x] = codeTab[tl.b * 256 + threadIdx.x];
+    __syncthreads();
     const uint32_t n = blkN[tl.b] - 8;
+    const uint32_t bits = symBits[tl.b], nch = h0[tl.b];
     const uint8_t *Tb = T + (size_t)tl.b * Tstride;
+    // element idx of the tile <-> p = pHi - idx
+    const uint32_t pHi = n - 1 - tl.lt * TILE, pLo = pHi - (tl.valid - 1);
+    for (uint32_t k = threadIdx.x; k < tl.valid + nch; k += TT) stext[k] = (pLo + k < n) ? scode[Tb[pLo + k]] : 0;
+    __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t idx = threadIdx.x + i * TT;
         if (idx < tl.valid) {
-            const uint32_t p = n - 1 - (tl.lt * TILE + idx);
-            uint64_t le = load_u64_unaligned(Tb + p);
-            uint64_t be = __byte_perm((uint32_t)(le >> 32), 0, 0x0123) |
-                          ((uint64_t)__byte_perm((uint32_t)le, 0, 0x0123) << 32);
-            const uint32_t have = n - p;  // bytes of the suffix
-            if (have < 8) be &= ~0ull << (8 * (8 - have));
-            const uint64_t kf = be >> (8 * (8 - nchars));
+            const uint32_t p = pHi - idx;
+            const uint16_t *sp = stext + (p - pLo);
+            uint64_t kf = 0;
+            for (uint32_t c = 0; c < nch; c++) kf = (kf << bits) | sp[c];
             if (PACKED) {
                 keys[tl.first + idx] = (kf << logS) | p;
             } else {
                 keys[tl.first + idx] = kf;
                 vals[tl.first + idx] = p;
             }
-            for (int ps = 0; ps < nchars; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
+            for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
         }
     }
     __syncthreads();
-    hist_flush(sh, nchars, hist, tl.b);
+    hist_flush(sh, passes, hist, tl.b);
 }
 
-// Doubling round: the list holds (group, -, p); second = 1 + local group id of
-// suffix p+h, 0 past the end.
+// Doubling round of the global path: the list holds (group, -, p); second = 1 +
+// group id of suffix p+h, 0 past the end; h = h0[b] << (round - 1).
 template <bool PACKED>
-__global__ void __launch_bounds__(TT) k_build(const uint32_t *__restrict__ rank, const uint32_t *__restrict__ blkN,
-                                              ListView lv, int logS, uint32_t h, int passes,
-                                              uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+__global__ void __launch_bounds__(TT) k_build(const uint64_t *__restrict__ rank, const uint32_t *__restrict__ blkN,
+                                              ListView lv, int logS, const uint32_t *__restrict__ h0, uint32_t round,
+                                              int passes, uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
                                               uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t sh[MAXP * 256];
@@ -228,8 +345,9 @@ __global__ void __launch_bounds__(TT) k_build(const uint32_t *__restrict__ rank,
     __syncthreads();
     const TileLoc tl = locate(lv, blockIdx.x);
     const uint32_t n = blkN[tl.b] - 8;
+    const uint32_t h = h0[tl.b] << (round - 1);
     const uint32_t Smask = (1u << logS) - 1;
-    const uint32_t *rk = rank + ((size_t)tl.b << logS);
+    const uint64_t *rk = rank + ((size_t)tl.b << logS);
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t idx = threadIdx.x + i * TT;
@@ -239,7 +357,7 @@ __global__ void __launch_bounds__(TT) k_build(const uint32_t *__restrict__ rank,
             if (PACKED) { p = (uint32_t)e & Smask; prim = (uint32_t)(e >> (2 * logS)); }
             else { p = vals[tl.first + idx]; prim = (uint32_t)(e >> logS); }
             uint32_t sec = 0;
-            if (p + h < n) sec = (rk[p + h] & Smask) + 1;
+            if (p + h < n) sec = rk_read(rk[p + h], round) + 1;
             const uint64_t kf = ((uint64_t)prim << logS) | sec;
             keys[tl.first + idx] = PACKED ? ((kf << logS) | p) : kf;
             for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
@@ -606,9 +724,11 @@ template <bool PACKED, bool ROUND0>
 __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
                                                      ListView lv, int logS, const uint32_t *__restrict__ aggHead,
                                                      const uint32_t *__restrict__ aggPst,
-                                                     const uint32_t *__restrict__ aggKeep, uint32_t *__restrict__ rank,
-                                                     uint32_t *__restrict__ SA, uint64_t *__restrict__ keysOut,
-                                                     uint32_t *__restrict__ valsOut, uint32_t *__restrict__ cntNext)
+                                                     const uint32_t *__restrict__ aggKeep, uint32_t round,
+                                                     uint64_t *__restrict__ rank, uint32_t *__restrict__ SA,
+                                                     uint64_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut,
+                                                     const uint32_t *__restrict__ cntBefore,
+                                                     uint32_t *__restrict__ cntNext)
 {
     __shared__ HK scratch[WARPS + 1];
     const TileLoc tl = locate(lv, blockIdx.x);
@@ -632,8 +752,11 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
     HK ex = hk_block_excl(v, &agg, scratch);
     ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, ex);
     if (threadIdx.x == 0 && agg.keep) atomicAdd(&cntNext[tl.b], agg.keep);
-    uint32_t curHead = ex.head, curPst = ex.pst, outPos = ex.keep;
+    // survivors are appended, in list order, behind what the block's next list already
+    // holds (cntBefore: a snapshot taken before this launch; null = nothing)
     const size_t gb = (size_t)tl.b << logS;
+    uint32_t curHead = ex.head, curPst = ex.pst;
+    uint32_t outPos = (uint32_t)gb + (cntBefore ? cntBefore[tl.b] : 0u) + (ex.keep - aggKeep[lv.tileBase[tl.b]]);
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         if (i0 + i < tl.valid) {
@@ -644,7 +767,7 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
             if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
             else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
             const uint32_t r = prim + (curHead - curPst);  // SA slot of the group head
-            rank[gb + p] = (uint32_t)gb | r;
+            rank[gb + p] = rk_make(round, prim, r);
             if (head[i] && head[i + 1]) {
                 SA[gb + r] = p;
             } else {
@@ -658,6 +781,290 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
             }
         }
     }
+}
+
+// ---- the local path ------------------------------------------------------------------
+// One CTA per window of LTILE list elements.  Groups are contiguous in the list
+// (in no particular order), so a group either lies inside the window - it is
+// then sorted by (group, second), re-ranked and compacted right here - or it
+// crosses a window boundary and its elements are forwarded, with their keys
+// built, to the global path's list.
+
+__device__ __forceinline__ int lphys(int j) { return j + j / LITEMS; }  // bank-conflict-free blocked access
+
+__device__ __forceinline__ void cex(uint64_t &a, uint64_t &b)
+{
+    const bool sw = b < a;
+    const uint64_t lo = sw ? b : a, hi = sw ? a : b;
+    a = lo;
+    b = hi;
+}
+
+// bitonic sorting network on N registers (N a power of two), ascending
+template <int N>
+__device__ __forceinline__ void sort_network(uint64_t (&k)[N])
+{
+#pragma unroll
+    for (int sz = 2; sz <= N; sz <<= 1) {
+#pragma unroll
+        for (int j = sz >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+                const int l = i ^ j;
+                if (l > i) {
+                    if ((i & sz) == 0) cex(k[i], k[l]);
+                    else cex(k[l], k[i]);
+                }
+            }
+        }
+    }
+}
+
+struct HK3 { uint32_t head, pst, keep; };  // head/pst: window index + 1 of the last flagged element (0 none)
+
+__global__ void __launch_bounds__(LT) k_local(const uint64_t *__restrict__ keysIn, ListView lv,
+                                              const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ h0,
+                                              int logS, uint32_t round, int passes, uint64_t *__restrict__ rank,
+                                              uint32_t *__restrict__ SA, uint64_t *__restrict__ outS,
+                                              uint32_t *__restrict__ cntS, uint64_t *__restrict__ outL,
+                                              uint32_t *__restrict__ cntL, uint32_t *__restrict__ hist)
+{
+    constexpr int W = LTILE, NW = LT / 32;
+    __shared__ __align__(16) uint64_t sk[W + W / LITEMS + 2];
+    __shared__ uint32_t sh[MAXP * 256];
+    __shared__ HK3 swarp[NW + 1];
+    __shared__ uint32_t s_misc[8];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const TileLoc tl = locate(lv, blockIdx.x);
+    const uint32_t n = blkN[tl.b] - 8;
+    const uint32_t h = h0[tl.b] << (round - 1);
+    const uint32_t Smask = (1u << logS) - 1;
+    const size_t gb = (size_t)tl.b << logS;
+    const uint64_t *rk = rank + gb;
+    const int valid = (int)tl.valid;
+
+    // load (coalesced), build the key, park in shared memory
+    {
+        uint64_t e[LITEMS];
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = i * LT + tid;
+            e[i] = (j < valid) ? keysIn[tl.first + j] : ~0ull;
+        }
+        uint64_t rv[LITEMS];
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const uint32_t q = ((uint32_t)e[i] & Smask) + h;
+            rv[i] = (e[i] != ~0ull && q < n) ? rk[q] : ~0ull;
+        }
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = i * LT + tid;
+            uint64_t key = ~0ull;
+            if (e[i] != ~0ull) {
+                const uint32_t p = (uint32_t)e[i] & Smask;
+                const uint32_t sec = (p + h < n) ? rk_read(rv[i], round) + 1u : 0u;
+                key = ((e[i] >> (2 * logS)) << (2 * logS)) | ((uint64_t)sec << logS) | p;
+            }
+            sk[lphys(j)] = key;
+        }
+    }
+    if (tid == 0) {
+        const uint32_t segCnt = lv.cnt[tl.b];
+        uint32_t prevG = 0xffffffffu, nextG = 0xffffffffu;
+        if (tl.lt > 0) prevG = (uint32_t)(keysIn[tl.first - 1] >> (2 * logS));
+        if (tl.lt * (uint32_t)W + tl.valid < segCnt) nextG = (uint32_t)(keysIn[tl.first + valid] >> (2 * logS));
+        s_misc[0] = prevG;
+        s_misc[1] = nextG;
+    }
+    __syncthreads();
+    // crossing groups: a prefix [0, lo) and a suffix [hi, valid) of the window
+    if (warp == 0) {
+        const uint32_t gFirst = (uint32_t)(sk[lphys(0)] >> (2 * logS));
+        const uint32_t gLast = (uint32_t)(sk[lphys(valid - 1)] >> (2 * logS));
+        int lo = 0, hi = valid;
+        if (s_misc[0] == gFirst) {  // first j with group > gFirst
+            int a = 0, b = valid;
+            while (a < b) {
+                const int m = (a + b) >> 1;
+                if ((uint32_t)(sk[lphys(m)] >> (2 * logS)) == gFirst) a = m + 1; else b = m;
+            }
+            lo = a;
+        }
+        if (s_misc[1] == gLast) {   // first j with group == gLast
+            int a = 0, b = valid;
+            while (a < b) {
+                const int m = (a + b) >> 1;
+                if ((uint32_t)(sk[lphys(m)] >> (2 * logS)) != gLast) a = m + 1; else b = m;
+            }
+            hi = a;
+        }
+        if (hi < lo) hi = lo;
+        if (lane == 0) {
+            const uint32_t nCross = (uint32_t)(lo + valid - hi);
+            s_misc[2] = lo;
+            s_misc[3] = hi;
+            s_misc[4] = nCross ? atomicAdd(&cntL[tl.b], nCross) : 0u;
+        }
+    }
+    __syncthreads();
+    int lo = (int)s_misc[2], hi = (int)s_misc[3];
+    const uint32_t lbase = s_misc[4];
+    if (lo + valid - hi > 0) {
+        for (int i = tid; i < passes * 256; i += LT) sh[i] = 0;
+        __syncthreads();
+        const int nCross = lo + valid - hi;
+        for (int idx = tid; idx < nCross; idx += LT) {
+            const int j = (idx < lo) ? idx : hi + (idx - lo);
+            const uint64_t key = sk[lphys(j)];
+            outL[gb + lbase + idx] = key;
+            const uint64_t kf = key >> logS;
+            for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
+        }
+        __syncthreads();
+        hist_flush(sh, passes, hist, tl.b);
+        // the bag is in no particular group order: forwarded elements become padding so
+        // that the sort leaves exactly the window's own groups in [0, hi - lo)
+        for (int idx = tid; idx < nCross; idx += LT) sk[lphys((idx < lo) ? idx : hi + (idx - lo))] = ~0ull;
+        __syncthreads();
+    }
+    if (s_misc[2] >= s_misc[3]) return;
+
+    hi -= lo;
+    lo = 0;
+    // sort the window by (group, second, p): blocked registers, network, merges
+    uint64_t k[LITEMS];
+#pragma unroll
+    for (int i = 0; i < LITEMS; i++) k[i] = sk[lphys(tid * LITEMS + i)];
+    sort_network<LITEMS>(k);
+#pragma unroll 1
+    for (int width = 1; width < LT; width <<= 1) {
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
+        __syncthreads();
+        const int pairFirst = tid & ~(2 * width - 1);
+        const int aBeg = pairFirst * LITEMS, bBeg = aBeg + width * LITEMS, bEnd = bBeg + width * LITEMS;
+        if (sk[lphys(bBeg - 1)] > sk[lphys(bBeg)]) {   // otherwise the two runs are already in order
+            const int diag = (tid - pairFirst) * LITEMS;
+            const int len = width * LITEMS;
+            int a = max(0, diag - len), b = min(diag, len);
+            while (a < b) {
+                const int m = (a + b) >> 1;
+                if (sk[lphys(aBeg + m)] <= sk[lphys(bBeg + diag - 1 - m)]) a = m + 1; else b = m;
+            }
+            int ai = aBeg + a, bi = bBeg + diag - a;
+            uint64_t ka = sk[lphys(ai)], kb = sk[lphys(min(bi, W - 1))];
+#pragma unroll
+            for (int i = 0; i < LITEMS; i++) {
+                const bool takeB = (bi < bEnd) && (ai >= bBeg || kb < ka);
+                k[i] = takeB ? kb : ka;
+                if (takeB) { bi++; kb = sk[lphys(min(bi, W - 1))]; }
+                else { ai++; ka = sk[lphys(min(ai, W - 1))]; }
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
+    __syncthreads();
+
+    // re-rank inside the window: flags, scan, new group ids
+    const int j0 = tid * LITEMS;
+    uint64_t prevKf = (j0 > 0) ? (sk[lphys(j0 - 1)] >> logS) : 0;
+    const uint64_t nextKf = (j0 + LITEMS < W) ? (sk[lphys(j0 + LITEMS)] >> logS) : ~0ull;
+    const uint64_t secMask = ((uint64_t)1 << logS) - 1;
+    uint32_t headBits = 0, pstBits = 0;   // bit i: element i of this thread; bit LITEMS: the next element
+#pragma unroll
+    for (int i = 0; i <= LITEMS; i++) {
+        const int j = j0 + i;
+        const uint64_t cur = (i < LITEMS) ? (k[i] >> logS) : nextKf;
+        bool hd, ps;
+        if (j >= hi) { hd = true; ps = true; }
+        else {
+            hd = (j == lo) || prevKf != cur || (cur & secMask) == 0;
+            ps = (j == lo) || (prevKf >> logS) != (cur >> logS);
+        }
+        headBits |= (uint32_t)hd << i;
+        pstBits |= (uint32_t)ps << i;
+        prevKf = cur;
+    }
+    HK3 v = {0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < LITEMS; i++) {
+        const int j = j0 + i;
+        if (j >= lo && j < hi) {
+            if ((headBits >> i) & 1u) v.head = j + 1;
+            if ((pstBits >> i) & 1u) v.pst = j + 1;
+            if (!(((headBits >> i) & 1u) && ((headBits >> (i + 1)) & 1u))) v.keep++;
+        }
+    }
+    // block-wide exclusive scan of (last head, last pst, keep)
+    HK3 inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t th = __shfl_up_sync(0xffffffffu, inc.head, o);
+        const uint32_t tp = __shfl_up_sync(0xffffffffu, inc.pst, o);
+        const uint32_t tk = __shfl_up_sync(0xffffffffu, inc.keep, o);
+        if (lane >= o) {
+            if (!inc.head) inc.head = th;
+            if (!inc.pst) inc.pst = tp;
+            inc.keep += tk;
+        }
+    }
+    if (lane == 31) swarp[warp] = inc;
+    __syncthreads();
+    if (tid == 0) {
+        HK3 s = {0, 0, 0};
+        for (int w = 0; w < NW; w++) {
+            const HK3 c = swarp[w];
+            swarp[w] = s;
+            if (c.head) s.head = c.head;
+            if (c.pst) s.pst = c.pst;
+            s.keep += c.keep;
+        }
+        swarp[NW] = s;
+        s_misc[5] = s.keep ? atomicAdd(&cntS[tl.b], s.keep) : 0u;
+    }
+    __syncthreads();
+    HK3 ex;
+    ex.head = __shfl_up_sync(0xffffffffu, inc.head, 1);
+    ex.pst = __shfl_up_sync(0xffffffffu, inc.pst, 1);
+    ex.keep = __shfl_up_sync(0xffffffffu, inc.keep, 1);
+    if (lane == 0) ex = HK3{0, 0, 0};
+    {
+        const HK3 wp = swarp[warp];
+        if (!ex.head) ex.head = wp.head;
+        if (!ex.pst) ex.pst = wp.pst;
+        ex.keep += wp.keep;
+    }
+    const uint32_t totalKeep = swarp[NW].keep;
+    const uint32_t sbase = s_misc[5];
+    __syncthreads();   // everyone has read the sorted neighbours: sk can take the survivors
+
+    uint32_t curHead = ex.head, curPst = ex.pst, outIdx = ex.keep;
+#pragma unroll
+    for (int i = 0; i < LITEMS; i++) {
+        const int j = j0 + i;
+        if (j >= lo && j < hi) {
+            const bool hd = (headBits >> i) & 1u, hn = (headBits >> (i + 1)) & 1u;
+            if (hd) curHead = j + 1;
+            if ((pstBits >> i) & 1u) curPst = j + 1;
+            const uint32_t p = (uint32_t)k[i] & Smask;
+            const uint32_t grp = (uint32_t)(k[i] >> (2 * logS));
+            const uint32_t r = grp + (curHead - curPst);
+            rank[gb + p] = rk_make(round, grp, r);
+            if (hd && hn) {
+                SA[gb + r] = p;
+            } else {
+                sk[outIdx] = ((uint64_t)r << (2 * logS)) | p;
+                outIdx++;
+            }
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < totalKeep; i += LT) outS[gb + sbase + i] = sk[i];
 }
 
 }  // namespace
@@ -679,12 +1086,26 @@ struct SortCtx {
     const BatchDesc &bd;
     cudaStream_t st;
     LaunchCounter &lc;
-    bool packed;
     int matchAny;
-    int cur;       // keys[cur] holds the list
-    int lcur;      // list view index
-    uint32_t count, tiles;
+    float *msSort;
+    cudaEvent_t evA, evB;
+    uint64_t algBytes;
 };
+
+// SALZ_DEBUG_SYNC=1: synchronise after every stage and name the one that failed.
+int dbg(SortCtx &s, const char *what)
+{
+    static const bool on = getenv("SALZ_DEBUG_SYNC") != nullptr;
+    if (!on) return 0;
+    cudaError_t e = cudaStreamSynchronize(s.st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "salz_cuda: [debug] %s failed: %s\n", what, cudaGetErrorString(e));
+        return -1;
+    }
+    fprintf(stderr, "salz_cuda: [debug] %s ok\n", what);
+    return 0;
+}
 
 ListView view(const Workspace &ws, int i)
 {
@@ -696,121 +1117,230 @@ ListView view(const Workspace &ws, int i)
     return lv;
 }
 
+// Tile map of list view `v` (counts already in listCnt[v]); totals land in counters[2*slot..].
+void tilemap(SortCtx &s, int v, uint32_t tileElems, int slot)
+{
+    Workspace &ws = s.ws;
+    k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[v], s.bd.B, tileElems, s.bd.logS, ws.listBase[v], ws.tileBase[v],
+                                    ws.counters + 2 * slot);
+    k_tilefill<<<s.bd.B, 128, 0, s.st>>>(ws.listCnt[v], ws.listBase[v], ws.tileBase[v], tileElems, ws.tileDesc[v]);
+    s.lc.launches += 2;
+}
+
+int fetch_counters(SortCtx &s)
+{
+    CK(cudaMemcpyAsync(s.ws.h_counters, s.ws.counters, 16, cudaMemcpyDeviceToHost, s.st));
+    CK(cudaStreamSynchronize(s.st));
+    return 0;
+}
+
+// `passes` LSD passes over list view `v` (count elements in `tiles` tiles), starting
+// in keys[src]; the other buffer is keys[dst].  Returns the buffer holding the result.
 template <bool PACKED>
-int radix_sort(SortCtx &s, int passes, int shift0)
+int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, int shift0, int src, int dst)
 {
     Workspace &ws = s.ws;
     const size_t smem = PACKED ? SCATTER_SMEM_PACKED : SCATTER_SMEM_PAIRS;
-    const uint32_t grid = std::min<uint32_t>(s.tiles, (uint32_t)(s.ws.numSMs * SCATTER_MIN_CTAS));
+    const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SCATTER_MIN_CTAS));
+    if (s.msSort) CK(cudaEventRecord(s.evA, s.st));
     for (int ps = 0; ps < passes; ps++) {
-        CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)s.tiles + 1) * 256 * 4, s.st));
+        CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
         if (s.matchAny)
-            k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
-                                                              ws.vals[s.cur ^ 1], view(ws, s.lcur), s.tiles,
-                                                              shift0 + 8 * ps, ps, ws.digitBase, ws.tileState);
+            k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst], ws.vals[dst & 1],
+                                                              view(ws, v), tiles, shift0 + 8 * ps, ps, ws.digitBase,
+                                                              ws.tileState);
         else
-            k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], ws.keys[s.cur ^ 1],
-                                                               ws.vals[s.cur ^ 1], view(ws, s.lcur), s.tiles,
-                                                               shift0 + 8 * ps, ps, ws.digitBase, ws.tileState);
+            k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst],
+                                                               ws.vals[dst & 1], view(ws, v), tiles, shift0 + 8 * ps, ps,
+                                                               ws.digitBase, ws.tileState);
         s.lc.launches += 1;
         s.lc.sort_launches += 1;
-        s.lc.sort_elems += s.count;
-        s.lc.sort_bytes += (uint64_t)s.count * (PACKED ? 16 : 24);
-        s.cur ^= 1;
+        s.lc.sort_elems += count;
+        s.lc.sort_bytes += (uint64_t)count * (PACKED ? 16 : 24);
+        std::swap(src, dst);
+    }
+    if (s.msSort) CK(cudaEventRecord(s.evB, s.st));
+    CK(cudaGetLastError());
+    s.algBytes += (uint64_t)count * (PACKED ? 16 : 24) * passes;
+    if (dbg(s, "radix_sort")) return -1;
+    return src;
+}
+
+int add_sort_time(SortCtx &s)
+{
+    if (s.msSort) {
+        float ms;
+        CK(cudaEventElapsedTime(&ms, s.evA, s.evB));
+        *s.msSort += ms;
+    }
+    return 0;
+}
+
+// Re-rank the sorted list (view v, in keys[src]): finished suffixes go to SA, the
+// survivors are appended to keys[dst] behind cntBefore[b] elements per block and
+// counted into listCnt[vNext].
+template <bool PACKED, bool ROUND0>
+int rerank(SortCtx &s, int v, uint32_t count, uint32_t tiles, int src, int dst, uint32_t round,
+           const uint32_t *cntBefore, int vNext)
+{
+    Workspace &ws = s.ws;
+    const int logS = s.bd.logS;
+    const ListView lv = view(ws, v);
+    k_rerank_reduce<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], lv, logS, ws.aggHead, ws.aggPst, ws.aggKeep);
+    k_rerank_scan<<<1, 1024, 0, s.st>>>(ws.aggHead, ws.aggPst, ws.aggKeep, tiles);
+    k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, ws.aggHead, ws.aggPst,
+                                                           ws.aggKeep, round, ws.rank, ws.SA, ws.keys[dst],
+                                                           ws.vals[dst & 1], cntBefore, ws.listCnt[vNext]);
+    s.lc.launches += 3;
+    s.algBytes += (uint64_t)count * (PACKED ? 28 : 36);
+    CK(cudaGetLastError());
+    if (dbg(s, "rerank")) return -1;
+    return 0;
+}
+
+int alphabet(SortCtx &s, int fieldBits)
+{
+    Workspace &ws = s.ws;
+    const BatchDesc &bd = s.bd;
+    CK(cudaMemsetAsync(ws.alphaMask, 0, (size_t)bd.B * 32, s.st));
+    k_alphabet<<<dim3((bd.maxN + ALPHA_CHUNK - 1) / ALPHA_CHUNK, bd.B), 256, 0, s.st>>>(ws.T, bd.Tstride, ws.blkN,
+                                                                                        ws.alphaMask);
+    k_alpha_finish<<<bd.B, 256, 0, s.st>>>(ws.alphaMask, fieldBits, ws.codeTab, ws.symBits, ws.h0);
+    s.lc.launches += 2;
+    s.algBytes += bd.M;
+    if (dbg(s, "alphabet")) return -1;
+    return 0;
+}
+
+// Round 0 on list view 2 (every suffix of every block), result re-ranked into
+// keys[dstBuf] / listCnt[vNext].  Returns through count/tiles the sizes used.
+template <bool PACKED>
+int round0(SortCtx &s, int passes, int shift0, int vNext, int *bufOut)
+{
+    Workspace &ws = s.ws;
+    const BatchDesc &bd = s.bd;
+    const int logS = bd.logS;
+    const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
+    uint32_t tiles = 0;
+    for (int b = 0; b < bd.B; b++) tiles += (ws.h_blkN[b] - 8 + TILE - 1) / TILE;
+    if (alphabet(s, 2 * logS)) return -1;
+    k_first_counts<<<(bd.B + 255) / 256, 256, 0, s.st>>>(ws.blkN, bd.B, ws.listCnt[2]);
+    tilemap(s, 2, TILE, 0);
+    CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
+    k_init<PACKED><<<tiles, TT, 0, s.st>>>(ws.T, bd.Tstride, ws.blkN, view(ws, 2), logS, passes, ws.codeTab, ws.symBits,
+                                           ws.h0, ws.keys[0], ws.vals[0], ws.hist);
+    k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+    s.lc.launches += 3;
+    s.algBytes += (uint64_t)bd.M * (PACKED ? 9 : 13);
+    if (dbg(s, "k_init")) return -1;
+    const int res = radix_sort<PACKED>(s, 2, bd.M, tiles, passes, shift0, 0, 1);
+    if (res < 0) return -1;
+    CK(cudaMemsetAsync(ws.listCnt[vNext], 0, (size_t)bd.B * 4, s.st));
+    if (rerank<PACKED, true>(s, 2, bd.M, tiles, res, res ^ 1, 0, nullptr, vNext)) return -1;
+    *bufOut = res ^ 1;
+    return 0;
+}
+
+// PACKED batches: round 0, then rounds of k_local (+ the global path for the
+// groups that cross windows) until no suffix is left in the bag.
+int sa_build_local(SortCtx &s, int &rounds)
+{
+    Workspace &ws = s.ws;
+    const BatchDesc &bd = s.bd;
+    const int logS = bd.logS;
+    const int passes = (2 * logS + 7) / 8;
+    const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
+    int bufS = 0;
+    if (round0<true>(s, passes, logS, 0, &bufS)) return -1;
+    int vS = 0;
+    tilemap(s, vS, LTILE, 0);
+    if (fetch_counters(s)) return -1;
+    if (add_sort_time(s)) return -1;
+    uint32_t count = ws.h_counters[0], tiles = ws.h_counters[1];
+    rounds = 0;
+    uint32_t round = 1;
+    while (count > 0) {
+        if (round > 27) {
+            fprintf(stderr, "salz_cuda: prefix doubling failed to converge (round %u)\n", round);
+            return -1;
+        }
+        // buffers: the bag is in keys[bufS]; the other two take the next bag and the global list
+        const int bufOut = (bufS + 1) % 3, bufL = (bufS + 2) % 3;
+        const int vNext = vS ^ 1;
+        CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
+        CK(cudaMemsetAsync(ws.listCnt[vNext], 0, (size_t)bd.B * 4, s.st));
+        CK(cudaMemsetAsync(ws.listCnt[2], 0, (size_t)bd.B * 4, s.st));
+        k_local<<<tiles, LT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, round, passes, ws.rank, ws.SA,
+                                        ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.listCnt[2], ws.hist);
+        s.lc.launches += 1;
+        s.algBytes += (uint64_t)count * 32;
+        if (dbg(s, "k_local")) return -1;
+        tilemap(s, vNext, LTILE, 0);
+        tilemap(s, 2, TILE, 1);
+        if (fetch_counters(s)) return -1;
+        const uint32_t countL = ws.h_counters[2], tilesL = ws.h_counters[3];
+        if (countL > 0) {
+            k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+            s.lc.launches += 1;
+            const int res = radix_sort<true>(s, 2, countL, tilesL, passes, logS, bufL, bufS);
+            if (res < 0) return -1;
+            CK(cudaMemcpyAsync(ws.cntSnap, ws.listCnt[vNext], (size_t)bd.B * 4, cudaMemcpyDeviceToDevice, s.st));
+            if (rerank<true, false>(s, 2, countL, tilesL, res, bufOut, round, ws.cntSnap, vNext)) return -1;
+            tilemap(s, vNext, LTILE, 0);
+            if (fetch_counters(s)) return -1;
+            if (add_sort_time(s)) return -1;
+        }
+        count = ws.h_counters[0];
+        tiles = ws.h_counters[1];
+        bufS = bufOut;
+        vS = vNext;
+        round++;
+        rounds++;
     }
     CK(cudaGetLastError());
     return 0;
 }
 
-// Re-rank the sorted list, write finished suffixes to SA, compact the rest into
-// the other key buffer and build the next round's list map.
-template <bool PACKED, bool ROUND0>
-int rerank(SortCtx &s)
-{
-    Workspace &ws = s.ws;
-    const int logS = s.bd.logS;
-    const int nxt = s.lcur ^ 1;
-    const ListView lv = view(ws, s.lcur);
-    k_rerank_reduce<PACKED, ROUND0><<<s.tiles, TT, 0, s.st>>>(ws.keys[s.cur], lv, logS, ws.aggHead, ws.aggPst, ws.aggKeep);
-    k_rerank_scan<<<1, 1024, 0, s.st>>>(ws.aggHead, ws.aggPst, ws.aggKeep, s.tiles);
-    CK(cudaMemsetAsync(ws.listCnt[nxt], 0, (size_t)s.bd.B * 4, s.st));
-    k_rerank_apply<PACKED, ROUND0><<<s.tiles, TT, 0, s.st>>>(ws.keys[s.cur], ws.vals[s.cur], lv, logS, ws.aggHead,
-                                                             ws.aggPst, ws.aggKeep, ws.rank, ws.SA, ws.keys[s.cur ^ 1],
-                                                             ws.vals[s.cur ^ 1], ws.listCnt[nxt]);
-    k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[nxt], s.bd.B, ws.listBase[nxt], ws.tileBase[nxt], ws.counters);
-    k_tilefill<<<s.bd.B, 128, 0, s.st>>>(ws.listCnt[nxt], ws.listBase[nxt], ws.tileBase[nxt], ws.tileDesc[nxt]);
-    s.lc.launches += 5;
-    CK(cudaMemcpyAsync(ws.h_counters, ws.counters, 8, cudaMemcpyDeviceToHost, s.st));
-    CK(cudaStreamSynchronize(s.st));
-    s.count = ws.h_counters[0];
-    s.tiles = ws.h_counters[1];
-    s.cur ^= 1;  // compacted list was written to the other buffer
-    s.lcur = nxt;
-    return 0;
-}
-
-template <bool PACKED>
-int sa_build_t(SortCtx &s, uint64_t &algBytes, int &rounds, float *msSort, cudaEvent_t evA, cudaEvent_t evB)
+// Block capacity above 2^21 (pairs format): every round re-sorts the whole list.
+int sa_build_pairs(SortCtx &s, int &rounds)
 {
     Workspace &ws = s.ws;
     const BatchDesc &bd = s.bd;
     const int logS = bd.logS;
-    static bool attrSet = false;
-    if (!attrSet) {
-        CK(cudaFuncSetAttribute(k_scatter<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
-        CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
-        CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
-        CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
-        attrSet = true;
-    }
-    const int elemBytes = PACKED ? 8 : 12;
-    int nchars = (2 * logS) / 8;
-    if (nchars > 8) nchars = 8;
-    const int passesD = (2 * logS + 7) / 8;
-    const int shift0 = PACKED ? logS : 0;
+    const int passes = (2 * logS + 7) / 8;
     const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
-
-    // round 0
-    k_first_counts<<<(bd.B + 255) / 256, 256, 0, s.st>>>(ws.blkN, bd.B, ws.listCnt[0]);
-    k_tilemap<<<1, 1024, 0, s.st>>>(ws.listCnt[0], bd.B, ws.listBase[0], ws.tileBase[0], ws.counters);
-    k_tilefill<<<bd.B, 128, 0, s.st>>>(ws.listCnt[0], ws.listBase[0], ws.tileBase[0], ws.tileDesc[0]);
-    CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
-    k_init<PACKED><<<s.tiles, TT, 0, s.st>>>(ws.T, bd.Tstride, ws.blkN, view(ws, 0), logS, nchars, ws.keys[0], ws.vals[0],
-                                             ws.hist);
-    k_scan_hist<<<dim3(nchars, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
-    s.lc.launches += 5;
-    algBytes += (uint64_t)s.count * (1 + elemBytes);
-    if (msSort) CK(cudaEventRecord(evA, s.st));
-    if (radix_sort<PACKED>(s, nchars, shift0)) return -1;
-    if (msSort) CK(cudaEventRecord(evB, s.st));
-    algBytes += (uint64_t)s.count * 2 * elemBytes * nchars;
-    uint32_t before = s.count;
-    if (rerank<PACKED, true>(s)) return -1;
-    if (msSort) { float ms; CK(cudaEventElapsedTime(&ms, evA, evB)); *msSort += ms; }
-    algBytes += (uint64_t)before * (2 * elemBytes + 4) + (uint64_t)s.count * elemBytes;
-
+    int cur = 0;
+    if (round0<false>(s, passes, 0, 0, &cur)) return -1;
+    int v = 0;
+    tilemap(s, v, TILE, 0);
+    if (fetch_counters(s)) return -1;
+    if (add_sort_time(s)) return -1;
+    uint32_t count = ws.h_counters[0], tiles = ws.h_counters[1];
     rounds = 0;
-    uint64_t h = (uint64_t)nchars;
-    while (s.count > 0) {
-        if (h >= bd.S) {
-            fprintf(stderr, "salz_cuda: prefix doubling failed to converge (h=%llu)\n", (unsigned long long)h);
+    uint32_t round = 1;
+    while (count > 0) {
+        if (round > 27) {
+            fprintf(stderr, "salz_cuda: prefix doubling failed to converge (round %u)\n", round);
             return -1;
         }
         CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
-        k_build<PACKED><<<s.tiles, TT, 0, s.st>>>(ws.rank, ws.blkN, view(ws, s.lcur), logS, (uint32_t)h, passesD,
-                                                  ws.keys[s.cur], ws.vals[s.cur], ws.hist);
-        k_scan_hist<<<dim3(passesD, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+        k_build<false><<<tiles, TT, 0, s.st>>>(ws.rank, ws.blkN, view(ws, v), logS, ws.h0, round, passes, ws.keys[cur],
+                                               ws.vals[cur], ws.hist);
+        k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
         s.lc.launches += 2;
-        algBytes += (uint64_t)s.count * (2 * elemBytes + 4);
-        if (msSort) CK(cudaEventRecord(evA, s.st));
-        if (radix_sort<PACKED>(s, passesD, shift0)) return -1;
-        if (msSort) CK(cudaEventRecord(evB, s.st));
-        algBytes += (uint64_t)s.count * 2 * elemBytes * passesD;
-        before = s.count;
-        if (rerank<PACKED, false>(s)) return -1;
-        if (msSort) { float ms; CK(cudaEventElapsedTime(&ms, evA, evB)); *msSort += ms; }
-        algBytes += (uint64_t)before * (2 * elemBytes + 4) + (uint64_t)s.count * elemBytes;
-        h *= 2;
+        s.algBytes += (uint64_t)count * 28;
+        const int res = radix_sort<false>(s, v, count, tiles, passes, 0, cur, cur ^ 1);
+        if (res < 0) return -1;
+        CK(cudaMemsetAsync(ws.listCnt[v ^ 1], 0, (size_t)bd.B * 4, s.st));
+        if (rerank<false, false>(s, v, count, tiles, res, res ^ 1, round, nullptr, v ^ 1)) return -1;
+        v ^= 1;
+        cur = res ^ 1;
+        tilemap(s, v, TILE, 0);
+        if (fetch_counters(s)) return -1;
+        if (add_sort_time(s)) return -1;
+        count = ws.h_counters[0];
+        tiles = ws.h_counters[1];
+        round++;
         rounds++;
     }
     CK(cudaGetLastError());
@@ -819,26 +1349,32 @@ int sa_build_t(SortCtx &s, uint64_t &algBytes, int &rounds, float *msSort, cudaE
 
 }  // namespace
 
-int sa_tile_elems() { return TILE; }
+int sa_tile_elems() { return TILE < LTILE ? TILE : LTILE; }
 
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st, LaunchCounter &lc,
              uint64_t &algBytes, int &rounds, float *msSort)
 {
     if (bd.M == 0) return 0;
-    cudaEvent_t evA = nullptr, evB = nullptr;
+    static bool attrSet = false;
+    if (!attrSet) {
+        CK(cudaFuncSetAttribute(k_scatter<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
+        CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
+        CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+        CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+        attrSet = true;
+    }
+    SortCtx s = {ws, bd, st, lc, sortMode == 0, msSort, nullptr, nullptr, 0};
     if (msSort) {
-        CK(cudaEventCreate(&evA));
-        CK(cudaEventCreate(&evB));
+        CK(cudaEventCreate(&s.evA));
+        CK(cudaEventCreate(&s.evB));
         *msSort = 0.f;
     }
-    uint32_t tiles = 0;
-    for (int b = 0; b < bd.B; b++) tiles += (ws.h_blkN[b] - 8 + TILE - 1) / TILE;
-    SortCtx s = {ws, bd, st, lc, 3 * bd.logS <= 64, sortMode == 0, 0, 0, bd.M, tiles};
-    int rc = s.packed ? sa_build_t<true>(s, algBytes, rounds, msSort, evA, evB)
-                      : sa_build_t<false>(s, algBytes, rounds, msSort, evA, evB);
+    const bool packed = 3 * bd.logS <= 64;
+    int rc = packed ? sa_build_local(s, rounds) : sa_build_pairs(s, rounds);
+    algBytes += s.algBytes;
     if (msSort) {
-        cudaEventDestroy(evA);
-        cudaEventDestroy(evB);
+        cudaEventDestroy(s.evA);
+        cudaEventDestroy(s.evB);
     }
     return rc;
 }

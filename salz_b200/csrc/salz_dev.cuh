@@ -35,15 +35,20 @@ struct Workspace {
     uint32_t *blkN;    // [Bmax]   N_b
 
     // suffix sorting (sa.cu)
-    uint64_t *keys[2];   // [Mcap] list elements (packed) or keys (pairs), double buffered
+    uint64_t *keys[3];   // [Mcap] list elements (packed) or keys (pairs); keys[2] aliases cand (packed only)
     uint32_t *vals[2];   // [Mcap] values of the pairs format (block capacity > 2^21 only)
-    uint32_t *rank;      // [Mcap] by g: padded global slot of the group head / final ISA
+    uint64_t *rank;      // [Mcap] by g: (stamp:8 | old:24 | new:24) block-local slot of the group head; new = final ISA
     uint32_t *SA;        // [Mcap] by slot: local text position p
-    uint32_t *listCnt[2];   // [Bmax]   list elements per block
-    uint32_t *listBase[2];  // [Bmax+1] list offset per block
-    uint32_t *tileBase[2];  // [Bmax+1] first tile per block
-    uint4 *tileDesc[2];     // [tileCap] (block, tile in block, first element, elements) of every tile
+    uint32_t *listCnt[3];   // [Bmax]   list elements per block (views 0/1: the bag / pairs list, 2: global path)
+    uint32_t *listBase[3];  // [Bmax+1] list offset per block (padded: b << logS)
+    uint32_t *tileBase[3];  // [Bmax+1] first tile per block
+    uint4 *tileDesc[3];     // [tileCap] (block, tile in block, first element, elements) of every tile
     size_t tileCap;
+    uint32_t *cntSnap;   // [Bmax] snapshot of a list count
+    uint32_t *alphaMask; // [Bmax][8] byte values present
+    uint16_t *codeTab;   // [Bmax][256] dense codes, from 1
+    uint32_t *symBits;   // [Bmax] bits per code
+    uint32_t *h0;        // [Bmax] characters compared by round 0
     uint32_t *hist;      // [Bmax][8][256] digit histograms for the coming sort
     uint32_t *digitBase; // [Bmax][8][256] exclusive scans of hist
     uint32_t *tileState; // [1 + tileCap][256]: ticket, then look-back states
