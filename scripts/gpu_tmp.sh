@@ -1,4 +1,10 @@
-nvidia-smi -L
-timeout 900 python -m pytest tests/test_multigpu.py tests/test_gpu.py -m gpu -x -q -k "two_gpu or linked" 2>&1 | tail -3
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 2 --warmup 1 --no-cpu-baseline 2>&1 | tail -3 | cut -c1-1500
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus 2 --steps 1 --warmup 1 2>&1 | tail -2 | cut -c1-600
+#!/bin/bash
+mkdir -p gpurun_out
+for mib in 64 128 256; do
+python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --mib $mib 2>&1 | python -c "
+import sys, json
+for l in sys.stdin:
+    if l.startswith('{'):
+        d = json.loads(l); print('mib $mib value %.1f' % d['value'], {k: round(v, 2) for k, v in d['extra']['stage_ms_per_step'].items()})
+"
+done 2>&1 | tee gpurun_out/tmp.txt
