@@ -130,7 +130,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
          dalloc(c, &ws.tilePreV, M / 4096 + 1) && dalloc(c, &ws.tileSufV, M / 4096 + 1);
     ok = ok && dalloc(c, &ws.cand, M + 64) && dalloc(c, &ws.cost, M + B + 64) && dalloc(c, &ws.choice, M);
     ws.keys[2] = (uint64_t *)ws.cand;  // the candidates are written after the suffix array is complete
-    ok = ok && dalloc(c, &ws.jump, M);
+    ok = ok && dalloc(c, &ws.jump, M + 64);
+    ok = ok && dalloc(c, &ws.segBase, B * 64) && dalloc(c, &ws.segDirty, B * 64) && dalloc(c, &ws.segChanged, B * 64);
     const size_t chunks = M >> PARSE_CHUNK_LOG;
     ok = ok && dalloc(c, &ws.chunkEntry, chunks) && dalloc(c, &ws.chunkTok, chunks) &&
          dalloc(c, &ws.chunkBits, chunks);
@@ -381,13 +382,15 @@ extern "C" int salz_cuda_debug_stages(salz_cuda_ctx *c, const uint8_t *src, size
     if (lcp) CKC(c, cudaMemcpy(lcp, ws.lcp, n * 4, cudaMemcpyDeviceToHost));
     if (cand) CKC(c, cudaMemcpy(cand, ws.cand, n * 16, cudaMemcpyDeviceToHost));
     if (parse) {
-        std::vector<int32_t> ch(2 * n), cs(n + 1);
+        // cost[p] (the reference's aux[4p+2]) = d[p] - 9p, d = relative value + segment base
+        std::vector<int32_t> ch(2 * n), cs(n + 1), sb(64);
         CKC(c, cudaMemcpy(ch.data(), ws.choice, n * 8, cudaMemcpyDeviceToHost));
         CKC(c, cudaMemcpy(cs.data(), ws.cost, (n + 1) * 4, cudaMemcpyDeviceToHost));
+        CKC(c, cudaMemcpy(sb.data(), ws.segBase, 64 * 4, cudaMemcpyDeviceToHost));
         for (size_t p = 0; p < n; p++) {
             parse[3 * p] = ch[2 * p];
             parse[3 * p + 1] = ch[2 * p + 1];
-            parse[3 * p + 2] = cs[p];
+            parse[3 * p + 2] = cs[p] + sb[p >> ws.parseSegLog] - 9 * (int32_t)p;
         }
     }
     if (dst && dst_len) {

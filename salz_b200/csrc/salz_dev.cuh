@@ -73,9 +73,12 @@ struct Workspace {
     int32_t *tileMinV, *tileMinL, *tilePreV, *tileSufV;
     // candidates / parse
     int4 *cand;        // [Mcap] by g
-    int32_t *cost;     // [Mcap + Bmax... ] by g, n_b entry = 0  (size Mcap + 64)
+    int32_t *cost;     // [Mcap + 64] by g: the parse's d values relative to the segment bases (parse.cu)
+    int parseSegLog;   // log2 of the segment length of the last parse
     int2 *choice;      // [Mcap] by g: (offs, len)
-    uint32_t *jump;    // [Mcap] by g: first position >= chunk end reached from p
+    uint32_t *jump;    // [Mcap] by g: first position >= chunk end reached from p 
+    int32_t *segBase;  // [Bmax][64] parse segments: d at the segment's right end
+    uint32_t *segDirty, *segChanged;  // [Bmax][64]
     // emit
     uint32_t *chunkEntry; // [Mcap / CHUNK]
     uint32_t *chunkTok;   // [Mcap / CHUNK] tokens starting in chunk -> exclusive prefix
