@@ -41,8 +41,17 @@ namespace {
 // costs matter and the optimal paths of neighbouring positions merge quickly.
 // K = 1 is the plain single pass (nothing is estimated).
 // ---------------------------------------------------------------------------
-constexpr int PC = 1024;           // positions per staged chunk (long enough to hide the helpers' memory latency)
-constexpr int HELPERS = 64;        // threads per helper group (stagers, finishers)
+#ifndef SALZ_PC
+#define SALZ_PC 1024
+#endif
+#ifndef SALZ_HELPERS
+#define SALZ_HELPERS 64
+#endif
+#ifndef SALZ_PARSE_CTAS
+#define SALZ_PARSE_CTAS 4
+#endif
+constexpr int PC = SALZ_PC;        // positions per staged chunk (long enough to hide the helpers' memory latency)
+constexpr int HELPERS = SALZ_HELPERS;  // threads per helper group (stagers, finishers)
 constexpr int PER = 8;             // positions a helper thread has in flight
 constexpr int SUBS = PC / (HELPERS * PER);  // batches of PER positions per helper thread and chunk
 constexpr int PARSE_WARPS = 1 + 2 * HELPERS / 32;
@@ -197,7 +206,7 @@ __device__ __forceinline__ void sts_i32(uint32_t addr, int32_t v)
 
 // grid = (K, B).  dr: d values by g, relative per segment; segBase / segChanged /
 // segDirty: [B][KMAX].
-__global__ void __launch_bounds__(PARSE_THREADS, 4) k_parse(const int4 *__restrict__ cand,
+__global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const int4 *__restrict__ cand,
                                                             const uint32_t *__restrict__ blkN, int logS, int segLog,
                                                             int numSMs, int32_t *dr, const int32_t *__restrict__ segBase,
                                                             const uint32_t *__restrict__ segDirty,
@@ -398,7 +407,7 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     int segLog = bd.logS, K = 1;
     {
         static const char *env = getenv("SALZ_PARSE_SEGMENTS");
-        const int slots = ws.numSMs * 4;
+        const int slots = ws.numSMs * SALZ_PARSE_CTAS;
         int want = env ? atoi(env) : slots / std::max(1, bd.B);
         if (!env && want < 4) want = 1;
         while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= 16u * PC) { K *= 2; segLog--; }

@@ -7,9 +7,10 @@ for l in sys.stdin:
         d = json.loads(l); print('$*', 'value %.1f' % d['value'], {k: round(v, 2) for k, v in d['extra']['stage_ms_per_step'].items()})
     elif 'rror' in l: print(l.rstrip())
 "; }
-run --mib 256
-run --mib 64
-SALZ_PARSE_SEGMENTS=1 run --mib 64
-run --mib 16
-SALZ_PARSE_SEGMENTS=1 run --mib 16
-run --workload english256 --level 9
+for v in variants/*.so; do
+  cp $v salz_b200/libsalz_cuda.so
+  echo "=== $v"
+  run --mib 256
+  SALZ_PARSE_SEGMENTS=4 run --mib 256
+  SALZ_PARSE_SEGMENTS=8 run --mib 256
+done
