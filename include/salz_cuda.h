@@ -133,6 +133,14 @@ void salz_cuda_reset_stats(salz_cuda_ctx *ctx);
  * mode 0           = warp peer masks by match_any. */
 void salz_cuda_set_sort_mode(salz_cuda_ctx *ctx, int mode);
 
+/* Segments per block of the optimal parse (replaces nothing in the reference:
+ * optimize_factorization, lib/salz.c:610-662, is one serial loop per block).
+ * 0 (default) = automatic: enough chains to fill the GPU when the batch has few
+ * blocks, one chain per block otherwise; k >= 1 = at most k segments (rounded
+ * down to a power of two, segments never shorter than 16384 positions).  The
+ * parse is exact for every k (the passes repeat until nothing changes). */
+void salz_cuda_set_parse_segments(salz_cuda_ctx *ctx, int k);
+
 /* Run this context's copies and kernels on the caller's CUDA stream
  * (a cudaStream_t passed as void *; NULL restores the context's own stream),
  * so that events the caller records on that stream bracket the work. */

@@ -18,7 +18,7 @@ EXPORTS = [
     "salz_cuda_device_count", "salz_cuda_ctx_create", "salz_cuda_ctx_destroy", "salz_cuda_last_error",
     "salz_cuda_encode_blocks", "salz_cuda_encode_stream", "salz_cuda_encode_stream_device",
     "salz_cuda_debug_stages", "salz_cuda_suffix_arrays", "salz_cuda_get_stats", "salz_cuda_reset_stats",
-    "salz_cuda_set_sort_mode", "salz_cuda_host_alloc", "salz_cuda_host_free", "salz_cuda_set_stream",
+    "salz_cuda_set_sort_mode", "salz_cuda_set_parse_segments", "salz_cuda_host_alloc", "salz_cuda_host_free", "salz_cuda_set_stream",
 ]
 
 
@@ -65,6 +65,7 @@ def load_library():
     L.salz_cuda_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.salz_cuda_reset_stats.argtypes = [C.c_void_p]
     L.salz_cuda_set_sort_mode.argtypes = [C.c_void_p, C.c_int]
+    L.salz_cuda_set_parse_segments.argtypes = [C.c_void_p, C.c_int]
     L.salz_cuda_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.salz_cuda_host_alloc.restype = C.c_void_p
     L.salz_cuda_host_alloc.argtypes = [C.c_size_t]
@@ -123,6 +124,10 @@ class SalzCuda:
 
     def set_sort_mode(self, mode):
         self.lib.salz_cuda_set_sort_mode(self.ctx, mode)
+
+    def set_parse_segments(self, k):
+        """Segments per block of the parse: 0 = automatic, k >= 1 = at most k."""
+        self.lib.salz_cuda_set_parse_segments(self.ctx, k)
 
     def set_stream(self, cuda_stream):
         """Run on the caller's stream (an int cudaStream_t, e.g. torch.cuda.Stream().cuda_stream)."""

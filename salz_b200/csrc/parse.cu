@@ -406,10 +406,9 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     // only pays when it is at least 4-fold (two passes + the confirming one).
     int segLog = bd.logS, K = 1;
     {
-        static const char *env = getenv("SALZ_PARSE_SEGMENTS");
         const int slots = ws.numSMs * SALZ_PARSE_CTAS;
-        int want = env ? atoi(env) : slots / std::max(1, bd.B);
-        if (!env && want < 4) want = 1;
+        int want = ws.parseSegments ? ws.parseSegments : slots / std::max(1, bd.B);
+        if (!ws.parseSegments && want < 4) want = 1;
         while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= 16u * PC) { K *= 2; segLog--; }
     }
     // cost holds d relative to the segment bases: cost[p] = dr[p] + segBase[p >> segLog] - 9p

@@ -75,6 +75,7 @@ struct Workspace {
     int4 *cand;        // [Mcap] by g
     int32_t *cost;     // [Mcap + 64] by g: the parse's d values relative to the segment bases (parse.cu)
     int parseSegLog;   // log2 of the segment length of the last parse
+    int parseSegments; // requested segments per block, 0 = automatic
     int2 *choice;      // [Mcap] by g: (offs, len)
     uint32_t *jump;    // [Mcap] by g: first position >= chunk end reached from p 
     int32_t *segBase;  // [Bmax][64] parse segments: d at the segment's right end

@@ -3,7 +3,7 @@
 Not the product and not the oracle: a slow, thread-by-thread transcription of
 what the kernels compute, used by the CPU test tier to check the *design*
 (prefix doubling with compaction, irreducible-PLCP fill, pyramid ANSV walk,
-windowed parse fixpoint, closed-form emit) against the oracle without a GPU.
+segmented shifted-cost parse, closed-form emit) against the oracle without a GPU.
 Only suitable for inputs of a few thousand bytes.
 """
 import numpy as np
@@ -14,62 +14,102 @@ CHUNK = 2048
 
 
 # ---------------------------------------------------------------- sa.cu ----
-def sa_model(blocks, logS=12):
-    """blocks: list of bytes objects (the n-byte texts to sort).  Returns list of SA arrays."""
-    S = 1 << logS
-    B = len(blocks)
-    bbits = max(0, (B - 1).bit_length())
-    h0 = min(8, (64 - bbits) // 8)
-    ns = [len(t) for t in blocks]
-    keys, vals, slots = [], [], []
-    for b, t in enumerate(blocks):
-        n = ns[b]
-        for r in range(n):          # descending position order inside a block
-            p = n - 1 - r
-            chunk = t[p:p + h0]
-            chunk = chunk + b"\0" * (h0 - len(chunk))
-            k = int.from_bytes(chunk, "big") | ((b << (8 * h0)) if h0 < 8 else 0)
-            keys.append(k); vals.append((b << logS) | p); slots.append((b << logS) | r)
-    rank = {}
-    SA = {}
-    rounds = 0
+def sa_model(blocks, logS=12, window=48, seed=0):
+    """Model of sa.cu for the packed format: dense codes from 1 (k_alphabet), round 0
+    on the first h0 characters, then rounds of k_local over windows of `window` list
+    elements (groups inside a window are sorted and re-ranked locally, groups that
+    cross a window boundary take the global path), u64-style stamped ranks read and
+    written in the same launch, and a bag whose chunks arrive in arbitrary order.
+    blocks: list of bytes objects (the n-byte texts).  Returns (list of SA arrays, rounds)."""
+    import random
+    rnd = random.Random(seed)
+    out, rounds_max = [], 0
+    for t in blocks:
+        n = len(t)
+        if n == 0:
+            out.append(np.zeros(0, np.int32)); continue
+        syms = sorted(set(t))
+        code = {c: i + 1 for i, c in enumerate(syms)}          # 0 = past the end
+        bits = max(1, len(syms).bit_length())
+        h0 = min(40, (2 * logS) // bits)
+        SA = [None] * n
+        rank = [None] * n                                        # (stamp, old, new)
 
-    def rerank(keys, vals, slots, sec_mask):
-        cnt = len(keys)
-        head = [k == 0 or keys[k] != keys[k - 1] or (sec_mask and (keys[k] & sec_mask) == 0)
-                for k in range(cnt)] + [True]
-        nv, nsl, npr = [], [], []
-        cur = None
-        for k in range(cnt):
-            if head[k]:
-                cur = slots[k]
-            rank[vals[k]] = cur
-            if head[k] and head[k + 1]:
-                SA[slots[k]] = vals[k] & (S - 1)
-            else:
-                nv.append(vals[k]); nsl.append(slots[k]); npr.append(cur)
-        return nv, nsl, npr
+        def rerank(sorted_elems, rnd_no):
+            """sorted_elems: list of (group, sec, p) sorted by (group, sec); returns survivors in order."""
+            cnt = len(sorted_elems)
+            surv = []
+            k = 0
+            while k < cnt:
+                g = sorted_elems[k][0]
+                e = k
+                while e < cnt and sorted_elems[e][0] == g:
+                    e += 1
+                # old group [k, e): split by sec (sec == 0 is always its own head)
+                i = k
+                while i < e:
+                    j = i + 1
+                    if sorted_elems[i][1] != 0:
+                        while j < e and sorted_elems[j][1] == sorted_elems[i][1]:
+                            j += 1
+                    r = g + (i - k)
+                    for q in range(i, j):
+                        pp = sorted_elems[q][2]
+                        rank[pp] = (rnd_no, g, r)
+                        if j - i == 1:
+                            SA[r] = pp
+                        else:
+                            surv.append((r, pp))
+                    i = j
+                k = e
+            return surv
 
-    order = sorted(range(len(keys)), key=lambda i: keys[i])  # python sort is stable
-    keys = [keys[i] for i in order]; vals = [vals[i] for i in order]
-    vals, slots, prim = rerank(keys, vals, slots, 0)
-    h = h0
-    while vals:
-        assert h < S, "no convergence"
-        keys = []
-        for k, g in enumerate(vals):
-            b, p = g >> logS, g & (S - 1)
-            sec = (rank[g + h] & (S - 1)) + 1 if p + h < ns[b] else 0
-            keys.append((prim[k] << logS) | sec)
-        order = sorted(range(len(keys)), key=lambda i: keys[i])
-        keys = [keys[i] for i in order]; vals = [vals[i] for i in order]
-        vals, slots, prim = rerank(keys, vals, slots, S - 1)
-        h *= 2
-        rounds += 1
-    out = []
-    for b in range(B):
-        out.append(np.array([SA[(b << logS) | r] for r in range(ns[b])], dtype=np.int32))
-    return out, rounds
+        # round 0: global sort on the code key
+        def key0(p):
+            k = 0
+            for c in range(h0):
+                k = (k << bits) | (code[t[p + c]] if p + c < n else 0)
+            return k
+        elems = sorted(((0, key0(p) + 1, p) for p in range(n)), key=lambda x: (x[0], x[1]))
+        # (+1 keeps "sec == 0 is a head" out of round 0: its keys are plain characters)
+        bag = rerank(elems, 0)
+        h, rnd_no = h0, 1
+        while bag:
+            assert h < (1 << logS), "no convergence"
+            def read(q):
+                st, old, new = rank[q]
+                return old if st == rnd_no else new
+            tiles = [bag[i:i + window] for i in range(0, len(bag), window)]
+            cross = []          # global-path list, pieces in arbitrary order
+            nxt_chunks = []
+            order = list(range(len(tiles)))
+            rnd.shuffle(order)  # CTAs run in any order: reads see a mix of refined and unrefined ranks
+            for ti in order:
+                tile = tiles[ti]
+                prevG = tiles[ti - 1][-1][0] if ti > 0 else None
+                nextG = tiles[ti + 1][0][0] if ti + 1 < len(tiles) else None
+                gF, gL = tile[0][0], tile[-1][0]
+                keyed = [(g, (read(pp + h) + 1) if pp + h < n else 0, pp) for g, pp in tile]
+                own, fwd = [], []
+                for e in keyed:
+                    if (prevG == gF and e[0] == gF) or (nextG == gL and e[0] == gL):
+                        fwd.append(e)
+                    else:
+                        own.append(e)
+                cross.append(fwd)
+                own.sort(key=lambda x: (x[0], x[1], x[2]))
+                nxt_chunks.append(rerank(own, rnd_no))
+            rnd.shuffle(cross)
+            glob = sorted((e for piece in cross for e in piece), key=lambda x: (x[0], x[1]))
+            nxt_chunks.append(rerank(glob, rnd_no))
+            rnd.shuffle(nxt_chunks)   # groups stay contiguous, their order is arbitrary
+            # the global path's survivors form ONE chunk: groups crossing rerank tiles stay contiguous
+            bag = [e for ch in nxt_chunks for e in ch]
+            h *= 2
+            rnd_no += 1
+        rounds_max = max(rounds_max, rnd_no - 1)
+        out.append(np.array(SA, dtype=np.int32))
+    return out, rounds_max
 
 
 # --------------------------------------------------------------- lcp.cu ----
@@ -182,82 +222,85 @@ def post_bits(l):
     return ((l - 3) >> 3) + 4
 
 
-def parse_model(cand, N):
-    """Window/lane transcription of k_parse.  Returns cost[n+1], choice[N,2], jump[N]."""
+def parse_model(cand, N, seg_len=256, seed=0):
+    """Model of k_parse / k_seg_scan: the chain in the shifted space d[p] = cost[p] + 9p
+    (one min per position), the block cut into segments of `seg_len` positions that
+    keep d relative to their right end, everything to the right of a segment read as
+    an estimate, passes (segments in arbitrary order, in place) until one changes
+    nothing.  Returns cost[n+1], choice[N,2], jump[N], passes."""
+    import random
+    rnd = random.Random(seed)
     n = N - 8
-    cost = np.zeros(N + 64, np.int64)
+    K = (N + seg_len - 1) // seg_len
+    dr = np.zeros(N + 1, np.int64)                 # relative d values, in place
+    base = np.full(K, 9 * n, np.int64)             # all-literal estimate; exact for the last segment
+    dirty = [True] * K
     choice = np.zeros((N, 2), np.int64)
-    jump = np.zeros(N, np.int64)
-    ring = np.zeros(CHUNK, np.int64)
-    cost_right = INF
-    iters_max = 0
-    for w in range((N - 1) >> 5, -1, -1):
-        q = (w << 5) + 31
-        P = [q - l for l in range(32)]
-        chunk_end = ((P[0] >> 11) + 1) << 11
-        a1 = [INF] * 32; a2 = [INF] * 32; l1 = [0] * 32; l2 = [0] * 32; o1 = [0] * 32; o2 = [0] * 32
-        f1 = [INF] * 32; f2 = [INF] * 32; n1 = [False] * 32; n2 = [False] * 32
-        x = [INF] * 32
-        for l, p in enumerate(P):
-            if 1 <= p < n:
+    choice[:, 1] = 1
+    w = {}                                         # factor weights minus 9 len
+    for p in range(1, n):
+        c = cand[p]
+        for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))):
+            if l >= 3:
+                w[(p, l, o)] = pre_bits(o) + 8 + post_bits(l) - 9 * l
+    passes = 0
+    while any(dirty):
+        passes += 1
+        assert passes <= K + 2, "segmented parse failed to settle"
+        changed = [False] * K
+        order = [j for j in range(K) if dirty[j]]
+        rnd.shuffle(order)
+        for j in order:
+            L, R = j * seg_len, min(N, (j + 1) * seg_len)
+
+            def dval(t):                           # relative to base[j]
+                return dr[t] if t < R else dr[t] + base[t // seg_len] - base[j]
+            d = INF if R == N else 0
+            new = {}
+            for p in range(R - 1, L - 1, -1):
+                if p > n:
+                    continue
+                m = 0 if p == n else INF
+                if 1 <= p < n:
+                    c = cand[p]
+                    for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))):
+                        if l >= 3:
+                            t = p + l
+                            v = new[t] if t < R else dval(t)
+                            m = min(m, v + w[(p, l, o)])
+                d = min(d, m)
+                new[p] = d
+            for p, v in new.items():
+                if dr[p] != v:
+                    changed[j] = True
+                    dr[p] = v
+            # finisher: the reference's comparisons in its order (literal, PSV, NSV; strict <)
+            for p in range(max(L, 1), min(R, n)):
                 c = cand[p]
-                if c[1] >= 3:
-                    o1[l], l1[l] = int(c[0]), int(c[1]); a1[l] = pre_bits(o1[l]) + 8 + post_bits(l1[l])
-                    if l1[l] <= l: n1[l] = True
-                    else: f1[l] = a1[l] + int(cost[p + l1[l]])
-                if c[3] >= 3:
-                    o2[l], l2[l] = int(c[2]), int(c[3]); a2[l] = pre_bits(o2[l]) + 8 + post_bits(l2[l])
-                    if l2[l] <= l: n2[l] = True
-                    else: f2[l] = a2[l] + int(cost[p + l2[l]])
-            x[l] = 0 if p == n else min(f1[l], f2[l])
-        xfar = list(x)
-        any_near = any(n1) or any(n2)
-        it = 0
-        while True:
-            it += 1
-            y = [x[l] - 9 * l for l in range(32)]
-            for l in range(1, 32):
-                y[l] = min(y[l], y[l - 1])
-            cst = [min(y[l] + 9 * l, cost_right + 9 * (l + 1)) for l in range(32)]
-            for l, p in enumerate(P):
-                if p > n: cst[l] = INF
-            if not any_near:
-                break
-            changed = False
-            for l in range(32):
-                nx = xfar[l]
-                if n1[l]: nx = min(nx, a1[l] + cst[l - l1[l]])
-                if n2[l]: nx = min(nx, a2[l] + cst[l - l2[l]])
-                if nx < x[l]: changed = True
-                x[l] = min(x[l], nx)
-            if not changed:
-                break
-        iters_max = max(iters_max, it)
-        t = [0] * 32
-        for l, p in enumerate(P):
-            right = cost_right if l == 0 else cst[l - 1]
-            c1 = a1[l] + cst[l - l1[l]] if n1[l] else f1[l]
-            c2 = a2[l] + cst[l - l2[l]] if n2[l] else f2[l]
-            best, bo, bl = 9 + right, 0, 1
-            if l1[l] >= 3 and c1 < best: best, bo, bl = c1, o1[l], l1[l]
-            if l2[l] >= 3 and c2 < best: best, bo, bl = c2, o2[l], l2[l]
-            if p == 0 or p >= n: bo, bl = 0, 1
-            t[l] = p + bl
-            if p < N:
-                if p <= n: cost[p] = cst[l]
+                best, bo, bl = dval(p + 1), 0, 1
+                for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))):
+                    if l >= 3:
+                        v = dval(p + l) + w[(p, l, o)]
+                        if v < best:
+                            best, bo, bl = v, o, l
                 choice[p] = (bo, bl)
-        for _ in range(5):
-            t = [t[q - t[l]] if (t[l] <= q and t[l] < N) else t[l] for l in range(32)]
-        for l, p in enumerate(P):
-            j = t[l]
-            if t[l] < chunk_end and t[l] < N:
-                j = ring[t[l] & (CHUNK - 1)]
-            t[l] = j
-        for l, p in enumerate(P):
-            ring[p & (CHUNK - 1)] = t[l]
-            if p < N: jump[p] = t[l]
-        cost_right = cst[31]
-    return cost[: n + 1], choice, jump, iters_max
+        # k_seg_scan
+        b = 9 * n
+        any_right = False
+        for j in range(K - 1, -1, -1):
+            base[j] = b
+            dirty[j] = any_right
+            any_right = any_right or changed[j]
+            b += dr[j * seg_len]
+        if K == 1:
+            break
+    cost = np.array([dr[p] + base[p // seg_len] - 9 * p for p in range(n + 1)], np.int64)
+    jump = np.zeros(N, np.int64)
+    for p in range(N - 1, -1, -1):
+        end = min(N, ((p >> 11) + 1) << 11)
+        t = p + int(choice[p][1])
+        jump[p] = t if t >= end else jump[t]
+    return cost, choice, jump, passes
 
 
 # -------------------------------------------------------------- emit.cu ----

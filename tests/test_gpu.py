@@ -109,6 +109,45 @@ def test_medium_cases_all_stages(enc, orc):
         _check_stages(enc, orc, name, data)
 
 
+@pytest.mark.parametrize("k", [1, 2, 8, 64])
+def test_parse_segments_exact_for_every_cut(enc, orc, k):
+    """The segmented parse (estimates to the right of a segment, passes until nothing
+    changes) must give the reference's (offs, len, cost) and bytes for any number of
+    segments, on text, deep repeats, one long factor and incompressible data."""
+    enc.set_parse_segments(k)
+    try:
+        cases = [("eng1M", synth.english_like(1 << 20, seed=11)),
+                 ("dna1M", synth.dna_like(1 << 20, seed=12)),
+                 ("a600k", np.full(600000, 0x61, np.uint8)),
+                 ("period7", np.resize(np.frombuffer(b"abcdefg", np.uint8), 300001)),
+                 ("rand300k", synth.uniform_random(300000, seed=13)),
+                 ("markov300k", synth.markov_text(300000, seed=42))]
+        for name, data in cases:
+            _check_stages(enc, orc, "%s/k%d" % (name, k), data)
+    finally:
+        enc.set_parse_segments(0)
+
+
+def test_alphabet_edge_cases(enc, orc):
+    """Round 0 sorts dense codes of the block's alphabet (1..sigma, 0 = past the end):
+    every sigma class, byte values 0 and 255, and suffixes that end inside the first key."""
+    rng = np.random.default_rng(21)
+    cases = [("sigma256", np.tile(np.arange(256, dtype=np.uint8), 40)),
+             ("sigma255", rng.integers(1, 256, 30000).astype(np.uint8)),
+             ("sigma2_0_255", rng.choice(np.array([0, 255], np.uint8), 40000)),
+             ("sigma3", rng.choice(np.array([0, 7, 200], np.uint8), 50000)),
+             ("sigma17", rng.integers(100, 117, 50000).astype(np.uint8)),
+             ("sigma33", rng.integers(0, 33, 50000).astype(np.uint8)),
+             ("zeros_tail", np.concatenate([rng.integers(0, 4, 20000).astype(np.uint8), np.zeros(64, np.uint8)])),
+             ("ff_run", np.full(5000, 255, np.uint8)),
+             ("short_keys", np.frombuffer(b"abracadabra" * 3, np.uint8))]
+    for name, data in cases:
+        _check_stages(enc, orc, name, data)
+    sas = enc.suffix_arrays([c[1] for c in cases])
+    for (name, data), sa in zip(cases, sas):
+        assert np.array_equal(sa, orc.suffix_array(data)), name
+
+
 def test_encode_blocks_error_semantics(enc, orc):
     """salz_encode_safe conventions (ref lib/salz.c:777-823)."""
     data = synth.english_like(5000, seed=3)
