@@ -23,43 +23,45 @@ namespace {
 // chunk (PC positions) ahead, in shared memory.  The consumer's ring loads for
 // position p-2 are issued before position p is finished (a factor is at least
 // 3 long, so they never wait on a value still being computed).
+//   flush(c+1)  ring -> global d array, by the stager warps
 //   stage(c-1)  consumer records of chunk c-1
-//   finish(c+1) the choice per position, recomputed from the final costs with
-//               the reference's comparison order (strict '<': literal, PSV,
-//               NSV; ref lib/salz.c:622-661), and written out
-//   flush(c)    ring -> global d array, by the helper warps
+// k_choose then derives the choice per position from the d array, fully parallel.
 //
 // Segments.  With few blocks in a batch one chain per block leaves the GPU
 // idle, so a block is cut into K segments of 2^segLog positions, one CTA each.
 // Every segment keeps d relative to its own right end (dr[p] = d[p] - base[j]);
 // what lies to the right of a segment is read as an ESTIMATE (the values other
 // CTAs have in dr[] at that moment plus the bases of the last scan).  Passes
-// are repeated until a pass changes nothing: then every segment was computed
-// from final values, and since the recurrence has exactly one solution that is
-// the reference's.  Pass i leaves at least the i rightmost segments exact (at
-// most K+1 passes); text-like inputs settle after two because only relative
+// are repeated until k_choose finds the recurrence satisfied at every position
+// (or a pass changes nothing): the recurrence has exactly one solution, so that
+// is the reference's.  Pass i leaves at least the i rightmost segments exact (at
+// most K+1 passes); text-like inputs are exact after two because only relative
 // costs matter and the optimal paths of neighbouring positions merge quickly.
 // K = 1 is the plain single pass (nothing is estimated).
 // ---------------------------------------------------------------------------
 #ifndef SALZ_PC
-#define SALZ_PC 1024
+#define SALZ_PC 512
 #endif
 #ifndef SALZ_HELPERS
 #define SALZ_HELPERS 64
 #endif
 #ifndef SALZ_PARSE_CTAS
-#define SALZ_PARSE_CTAS 4
+#define SALZ_PARSE_CTAS 2
 #endif
 constexpr int PC = SALZ_PC;        // positions per staged chunk (long enough to hide the helpers' memory latency)
-constexpr int HELPERS = SALZ_HELPERS;  // threads per helper group (stagers, finishers)
+constexpr int HELPERS = SALZ_HELPERS;  // stager threads
 constexpr int PER = 8;             // positions a helper thread has in flight
 constexpr int SUBS = PC / (HELPERS * PER);  // batches of PER positions per helper thread and chunk
-constexpr int PARSE_WARPS = 1 + 2 * HELPERS / 32;
-constexpr int PARSE_THREADS = 32 * PARSE_WARPS;  // consumer warp + stagers + finishers
+#ifndef SALZ_NCH
+#define SALZ_NCH 4
+#endif
+constexpr int NCH = SALZ_NCH;        // chains per CTA (lanes of the consumer warp are split between them)
+constexpr int PARSE_WARPS = 1 + NCH * HELPERS / 32;
+constexpr int PARSE_THREADS = 32 * PARSE_WARPS;  // consumer warp + stagers of every chain
 constexpr int NOT_FAR = -1;
 constexpr int RING = 2 * PC;       // ring entries; entry RING is a constant INF (absent edge)
 constexpr int KMAX = 64;           // segments per block, at most
-constexpr size_t PARSE_SMEM = 2 * PC * (sizeof(int4) + sizeof(uint32_t)) + (RING + 4) * sizeof(int32_t);
+constexpr size_t PARSE_SMEM = NCH * (2 * PC * (sizeof(int4) + sizeof(uint32_t)) + (RING + 4) * sizeof(int32_t));
 
 struct SegCtx {
     const int32_t *dr;     // block's d array, relative per segment
@@ -123,66 +125,21 @@ __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const S
   }
 }
 
-// Choices of a chunk whose d values (and every value to its right in the
-// segment) are in global memory: the reference's comparisons, in its order
-// (ref lib/salz.c:622-661), on d-space values (a common -9p drops out).
-__device__ __forceinline__ void finish_chunk(const int4 *__restrict__ cd, const SegCtx &sg, uint32_t N, uint32_t n,
-                                             uint32_t chunk, int2 *__restrict__ ch, int tid)
-{
-#pragma unroll 1
-  for (int sub = 0; sub < SUBS; sub++) {
-    const uint32_t base = chunk * PC + sub * (HELPERS * PER);
-    int4 c[PER];
-    int32_t r0[PER], r1[PER], r2[PER];
-#pragma unroll
-    for (int k = 0; k < PER; k++) {
-        const uint32_t p = base + tid + k * HELPERS;
-        c[k] = (p >= 1 && p < n) ? cd[p] : make_int4(0, 0, 0, 0);  // position 0 and the 8-byte tail are forced literals
-    }
-#pragma unroll
-    for (int k = 0; k < PER; k++) {  // all loads in flight together
-        const uint32_t p = base + tid + k * HELPERS;
-        const bool in = p >= 1 && p < n;
-        r0[k] = in ? dval(sg, p + 1) : 0;
-        r1[k] = (in && c[k].y >= 3) ? dval(sg, p + (uint32_t)c[k].y) : 0;
-        r2[k] = (in && c[k].w >= 3) ? dval(sg, p + (uint32_t)c[k].w) : 0;
-    }
-#pragma unroll
-    for (int k = 0; k < PER; k++) {
-        const uint32_t p = base + tid + k * HELPERS;
-        if (p >= N) break;
-        uint32_t bo = 0, bl = 1;
-        if (p >= 1 && p < n) {
-            int32_t best = r0[k];
-            if (c[k].y >= 3) {
-                const int32_t c1 = factor_cost_bits((uint32_t)c[k].x, (uint32_t)c[k].y) - 9 * c[k].y + r1[k];
-                if (c1 < best) { best = c1; bo = (uint32_t)c[k].x; bl = (uint32_t)c[k].y; }
-            }
-            if (c[k].w >= 3) {
-                const int32_t c2 = factor_cost_bits((uint32_t)c[k].z, (uint32_t)c[k].w) - 9 * c[k].w + r2[k];
-                if (c2 < best) { best = c2; bo = (uint32_t)c[k].z; bl = (uint32_t)c[k].w; }
-            }
-        }
-        ch[p] = make_int2((int)bo, (int)bl);
-    }
-  }
-}
-
-// ring -> global d array for chunk c (needed by stage(c-2) and finish(c)); ht in [0, 2 HELPERS).
+// ring -> global d array for chunk c (needed by stage(c-2) and k_choose); ht in [0, HELPERS).
 // Returns true when a value differs from what the array held.
 __device__ __forceinline__ bool flush_chunk(const int32_t *ring, int32_t *drb, uint32_t n, uint32_t c, int ht)
 {
-    constexpr int FP = PC / (2 * HELPERS);
+    constexpr int FP = PC / HELPERS;
     int32_t old[FP];
 #pragma unroll
     for (int k = 0; k < FP; k++) {
-        const uint32_t p = c * PC + ht + k * 2 * HELPERS;
+        const uint32_t p = c * PC + ht + k * HELPERS;
         old[k] = (p <= n) ? drb[p] : 0;
     }
     bool changed = false;
 #pragma unroll
     for (int k = 0; k < FP; k++) {
-        const int i = ht + k * 2 * HELPERS;
+        const int i = ht + k * HELPERS;
         const uint32_t p = c * PC + i;
         if (p <= n) {
             const int32_t v = ring[(c & 1u) * PC + i];
@@ -191,7 +148,7 @@ __device__ __forceinline__ bool flush_chunk(const int32_t *ring, int32_t *drb, u
     }
     return changed;
 }
-__device__ __forceinline__ void helper_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(2 * HELPERS) : "memory"); }
+__device__ __forceinline__ void helper_barrier(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(HELPERS) : "memory"); }
 
 __device__ __forceinline__ int32_t lds_i32(uint32_t addr)
 {
@@ -204,116 +161,168 @@ __device__ __forceinline__ void sts_i32(uint32_t addr, int32_t v)
     asm volatile("st.shared.s32 [%0], %1;" ::"r"(addr), "r"(v));
 }
 
-// grid = (K, B).  dr: d values by g, relative per segment; segBase / segChanged /
-// segDirty: [B][KMAX].
+// One CTA runs NCH chains: the consumer warp gives each chain 32 / NCH lanes (the lanes
+// of a chain run the same scalar recurrence; different chains share the instruction
+// stream, which is what the SM runs out of first), and every chain has its own
+// HELPERS stager threads, ring and record buffers.  Chain q = b * K + j is segment j of
+// block b; grid = ceil(B * K / NCH).  dr: d values by g, relative per segment;
+// segBase / segChanged / segDirty: [B][KMAX].
+struct Chain {
+    uint32_t b, j, N, n, R, cBeg, cEnd;
+    bool act, last;
+};
+
+__device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog, int segLog,
+                                          const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ segDirty)
+{
+    Chain ch;
+    ch.act = false;
+    ch.b = ch.j = ch.N = ch.n = ch.R = ch.cBeg = ch.cEnd = 0;
+    ch.last = false;
+    if (q >= chains) return ch;
+    ch.b = q >> kLog;
+    ch.j = q & ((1u << kLog) - 1);
+    ch.N = blkN[ch.b];
+    ch.n = ch.N - 8;
+    const uint32_t L = ch.j << segLog;
+    if (L >= ch.N) return ch;
+    if (!segDirty[ch.b * KMAX + ch.j]) return ch;  // nothing to the right changed since this segment was computed
+    ch.R = min(ch.N, L + (1u << segLog));
+    ch.last = ch.R == ch.N;
+    ch.cBeg = L / PC;
+    ch.cEnd = (ch.R + PC - 1) / PC;  // segment lengths are multiples of PC
+    ch.act = true;
+    return ch;
+}
+
 __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const int4 *__restrict__ cand,
                                                             const uint32_t *__restrict__ blkN, int logS, int segLog,
-                                                            int numSMs, int32_t *dr, const int32_t *__restrict__ segBase,
+                                                            int kLog, uint32_t chains, int numSMs, int32_t *dr,
+                                                            const int32_t *__restrict__ segBase,
                                                             const uint32_t *__restrict__ segDirty,
-                                                            uint32_t *__restrict__ segChanged,
-                                                            int2 *__restrict__ choice)
+                                                            uint32_t *__restrict__ segChanged)
 {
     extern __shared__ __align__(16) uint8_t psmem[];
-    int4 *stC = (int4 *)psmem;            // [2][PC] consumer records
-    uint32_t *stD = (uint32_t *)(stC + 2 * PC);  // [2][PC] second ring address
-    int32_t *ring = (int32_t *)(stD + 2 * PC);  // [RING + 1], d-space
-    __shared__ int32_t sbase[KMAX];
-    __shared__ uint32_t s_changed;
-    const uint32_t ringAddr = (uint32_t)__cvta_generic_to_shared(ring);
-    const uint32_t b = blockIdx.y, j = blockIdx.x;
-    const uint32_t N = blkN[b];
-    const uint32_t n = N - 8;
-    const uint32_t L = j << segLog;
-    if (L >= N) return;
-    if (!segDirty[b * KMAX + j]) return;  // nothing to the right changed since this segment was computed
-    const uint32_t R = min(N, L + (1u << segLog));
-    const bool last = R == N;
+    int4 *stC = (int4 *)psmem;                          // [NCH][2][PC] consumer records
+    uint32_t *stD = (uint32_t *)(stC + NCH * 2 * PC);   // [NCH][2][PC] second ring address
+    int32_t *rings = (int32_t *)(stD + NCH * 2 * PC);   // [NCH][RING + 4], d-space
+    __shared__ int32_t sbase[NCH][KMAX];
+    __shared__ uint32_t s_changed[NCH];
     // co-resident CTAs put their consumer on different warp slots
-    const uint32_t lin = blockIdx.x + blockIdx.y * gridDim.x;
+    const uint32_t lin = blockIdx.x;
     const int cw = (int)((lin + lin / (uint32_t)numSMs) % 4u);
     const int warp = ((int)(threadIdx.x >> 5) + PARSE_WARPS - cw) % PARSE_WARPS;  // role: 0 consumer, 1.. helpers
     const int lane = threadIdx.x & 31;
-    const int tid = warp * 32 + lane;
-    const size_t gb = (size_t)b << logS;
+    // the chain this thread works for
+    const int ci = (warp == 0) ? lane / (32 / NCH) : (warp - 1) / (HELPERS / 32);
+    const int ht = ((warp - 1) % (HELPERS / 32)) * 32 + lane;  // helper thread index inside the chain
+    const Chain ch = chain_of(blockIdx.x * NCH + ci, chains, kLog, segLog, blkN, segDirty);
+    uint32_t maxSteps = 0;
+#pragma unroll
+    for (int k = 0; k < NCH; k++) {
+        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN, segDirty);
+        if (o.act) maxSteps = max(maxSteps, o.cEnd - o.cBeg);
+    }
+    if (maxSteps == 0) return;
+
+    const size_t gb = (size_t)ch.b << logS;
     const int4 *cd = cand + gb;
     int32_t *drb = dr + gb;
-    int2 *ch = choice + gb;
+    int32_t *ring = rings + ci * (RING + 4);
+    int4 *myC = stC + ci * 2 * PC;
+    uint32_t *myD = stD + ci * 2 * PC;
+    const uint32_t ringAddr = (uint32_t)__cvta_generic_to_shared(ring);
 
-    if (threadIdx.x < KMAX) {
-        const uint32_t m = j + threadIdx.x;
-        sbase[threadIdx.x] = (m < KMAX && ((size_t)m << segLog) < N) ? segBase[b * KMAX + m] - segBase[b * KMAX + j] : 0;
+    for (int i = threadIdx.x; i < NCH * KMAX; i += PARSE_THREADS) {
+        const int k = i / KMAX;
+        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN, segDirty);
+        const uint32_t m = o.j + (uint32_t)(i % KMAX);
+        sbase[k][i % KMAX] = (o.act && m < KMAX && ((size_t)m << segLog) < o.N)
+                                 ? segBase[o.b * KMAX + m] - segBase[o.b * KMAX + o.j] : 0;
     }
-    if (threadIdx.x == 0) s_changed = 0;
-    for (int i = threadIdx.x; i <= RING; i += PARSE_THREADS) ring[i] = SALZ_INF;
+    if (threadIdx.x < NCH) s_changed[threadIdx.x] = 0;
+    for (int i = threadIdx.x; i < NCH * (RING + 4); i += PARSE_THREADS) rings[i] = SALZ_INF;
+    // lanes of a chain without work idle along with the others: their records must hold loadable addresses
+    {
+        const uint32_t anyRing = (uint32_t)__cvta_generic_to_shared(rings);
+        for (int i = threadIdx.x; i < NCH * 2 * PC; i += PARSE_THREADS) {
+            stC[i] = make_int4(SALZ_INF, 0, 0, (int)anyRing);
+            stD[i] = anyRing;
+        }
+    }
     __syncthreads();
-    SegCtx sg = {drb, sbase, R, j, segLog};
+    SegCtx sg = {drb, sbase[ci], ch.R, ch.j, segLog};
+    const uint32_t nch = ch.act ? ch.cEnd - ch.cBeg : 0;
 
-    const uint32_t cBeg = L / PC, cEnd = (R + PC - 1) / PC;  // segment lengths are multiples of PC
-    if (warp >= 1 && warp <= HELPERS / 32) {
-        const uint32_t c = cEnd - 1;
-        stage_chunk(cd, sg, n, c, stC + (c & 1) * PC, stD + (c & 1) * PC, ringAddr, tid - 32);
+    if (warp >= 1 && ch.act) {
+        const uint32_t c = ch.cEnd - 1;
+        stage_chunk(cd, sg, ch.n, c, myC + (c & 1) * PC, myD + (c & 1) * PC, ringAddr, ht);
     }
     __syncthreads();
 
-    int32_t d = last ? SALZ_INF : 0;  // d[p + 1] relative to the segment's base
+    int32_t d = ch.last ? SALZ_INF : 0;  // d[p + 1] relative to the segment's base
     bool changed = false;
-    for (uint32_t c = cEnd; c-- > cBeg;) {
+    // step s: the consumer walks chunk cEnd-1-s of every chain that still has one; the
+    // stagers flush the chunk it has just left and prepare the one after
+    for (uint32_t s = 0; s <= maxSteps; s++) {
+        const uint32_t c = ch.cEnd - 1 - min(s, nch ? nch - 1 : 0u);
         if (warp >= 1) {
-            // helpers: the chunk the consumer has just left goes to global memory first
-            if (c + 1 < cEnd) {
-                changed |= flush_chunk(ring, drb, n, c + 1, tid - 32);
-                helper_barrier();
+            if (ch.act && s >= 1 && s <= nch) {
+                changed |= flush_chunk(ring, drb, ch.n, ch.cEnd - s, ht);
+                helper_barrier(1 + ci);
             }
-            if (warp > HELPERS / 32) {
-                if (c + 1 < cEnd) finish_chunk(cd, sg, N, n, c + 1, ch, tid - 32 - HELPERS);
-            } else if (c > cBeg) {
-                stage_chunk(cd, sg, n, c - 1, stC + ((c - 1) & 1) * PC, stD + ((c - 1) & 1) * PC, ringAddr, tid - 32);
-            }
+            if (ch.act && s + 1 < nch)
+                stage_chunk(cd, sg, ch.n, c - 1, myC + ((c - 1) & 1) * PC, myD + ((c - 1) & 1) * PC, ringAddr, ht);
         } else {
-            const int4 *rc = stC + (c & 1) * PC;
-            const uint32_t *rd = stD + (c & 1) * PC;
-            // ring slot of position c*PC + i is ((c & 1) * PC + i)
-            const uint32_t slot0 = ringAddr + (c & 1u) * PC * 4;
-            int4 r0 = rc[PC - 1], r1 = rc[PC - 2];
-            int32_t a0 = lds_i32((uint32_t)r0.w), b0 = lds_i32(rd[PC - 1]);
-            int32_t a1 = lds_i32((uint32_t)r1.w), b1 = lds_i32(rd[PC - 2]);
-            // Records of positions i-2 .. i-9 are fetched one half-body ahead of their use;
-            // the ring loads of position j-2 go out before position j is finished (its
-            // targets are >= j+1: all stored).
-            int4 X[8], Y[8];
-            uint32_t XD[8], YD[8];
+            const bool live = s < nch;
+            if (__any_sync(0xffffffffu, live)) {
+                const int4 *rc = myC + (c & 1) * PC;
+                const uint32_t *rd = myD + (c & 1) * PC;
+                // ring slot of position c*PC + i is ((c & 1) * PC + i)
+                const uint32_t slot0 = ringAddr + (c & 1u) * PC * 4;
+                int4 r0 = rc[PC - 1], r1 = rc[PC - 2];
+                int32_t a0 = lds_i32((uint32_t)r0.w), b0 = lds_i32(rd[PC - 1]);
+                int32_t a1 = lds_i32((uint32_t)r1.w), b1 = lds_i32(rd[PC - 2]);
+                // Records of positions i-2 .. i-2-HB+1 are fetched one half-body ahead of their
+                // use; the ring loads of position j-2 go out before position j is finished (its
+                // targets are >= j+1: all stored).
+                constexpr int HB = 4;
+                int4 X[HB], Y[HB];
+                uint32_t XD[HB], YD[HB];
 #pragma unroll
-            for (int k = 0; k < 8; k++) { X[k] = rc[(PC - 3 - k) & (PC - 1)]; XD[k] = rd[(PC - 3 - k) & (PC - 1)]; }
-            auto half = [&](int4 (&use)[8], uint32_t (&useD)[8], int4 (&load)[8], uint32_t (&loadD)[8], int i) {
+                for (int k = 0; k < HB; k++) { X[k] = rc[(PC - 3 - k) & (PC - 1)]; XD[k] = rd[(PC - 3 - k) & (PC - 1)]; }
+                auto half = [&](int4 (&use)[HB], uint32_t (&useD)[HB], int4 (&load)[HB], uint32_t (&loadD)[HB], int i) {
 #pragma unroll
-                for (int k = 0; k < 8; k++) { load[k] = rc[(i - k - 10) & (PC - 1)]; loadD[k] = rd[(i - k - 10) & (PC - 1)]; }
+                    for (int k = 0; k < HB; k++) {
+                        load[k] = rc[(i - k - 2 - HB) & (PC - 1)];
+                        loadD[k] = rd[(i - k - 2 - HB) & (PC - 1)];
+                    }
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    const int4 r2 = use[k];
-                    const int32_t a2 = lds_i32((uint32_t)r2.w);
-                    const int32_t b2 = lds_i32(useD[k]);
-                    d = min(d, min(r0.x, min(a0 + r0.y, b0 + r0.z)));
-                    sts_i32(slot0 + (uint32_t)(i - k) * 4, d);  // every lane: same address, same value
-                    r0 = r1; a0 = a1; b0 = b1;
-                    r1 = r2; a1 = a2; b1 = b2;
-                }
-            };
+                    for (int k = 0; k < HB; k++) {
+                        const int4 r2 = use[k];
+                        const int32_t a2 = lds_i32((uint32_t)r2.w);
+                        const int32_t b2 = lds_i32(useD[k]);
+                        const int32_t nd = min(d, min(r0.x, min(a0 + r0.y, b0 + r0.z)));
+                        if (live) {  // a finished chain's lanes idle along (records may be stale)
+                            d = nd;
+                            sts_i32(slot0 + (uint32_t)(i - k) * 4, d);  // the chain's lanes: same address, same value
+                        }
+                        r0 = r1; a0 = a1; b0 = b1;
+                        r1 = r2; a1 = a2; b1 = b2;
+                    }
+                };
 #pragma unroll 1
-            for (int i = PC - 1; i >= 0; i -= 16) {
-                half(X, XD, Y, YD, i);
-                half(Y, YD, X, XD, i - 8);
+                for (int i = PC - 1; i >= 0; i -= 2 * HB) {
+                    half(X, XD, Y, YD, i);
+                    half(Y, YD, X, XD, i - HB);
+                }
             }
         }
         __syncthreads();
     }
-    if (warp >= 1) {
-        changed |= flush_chunk(ring, drb, n, cBeg, tid - 32);
-        helper_barrier();
-        if (warp > HELPERS / 32) finish_chunk(cd, sg, N, n, cBeg, ch, tid - 32 - HELPERS);
-    }
-    if (changed) s_changed = 1;
+    if (warp >= 1 && changed) s_changed[ci] = 1;
     __syncthreads();
-    if (threadIdx.x == 0) segChanged[b * KMAX + j] = s_changed;
+    if (warp >= 1 && ht == 0 && ch.act) segChanged[ch.b * KMAX + ch.j] = s_changed[ci];
 }
 
 // Before the first pass: every base = 9 n_b (the all-literal estimate in d-space,
@@ -351,6 +360,54 @@ __global__ void k_seg_scan(const uint32_t *__restrict__ blkN, int B, int logS, i
         base += drb[(size_t)j << segLog];  // d at the first position of segment j = base of segment j-1
     }
     if (dirty) atomicAdd(&counters[8], dirty);
+}
+
+// The choice per position from the d values in global memory, with the reference's
+// comparisons in its order (strict '<': literal, PSV, NSV; ref lib/salz.c:622-661; a
+// common -9p drops out in d-space) - and at the same time the proof that the values
+// are final: every position's recurrence must hold on the stored values.  The
+// recurrence is evaluated right to left over a DAG, so an array that satisfies it
+// everywhere IS its one solution, however it was arrived at.  counters[9] += misses.
+__global__ void __launch_bounds__(256) k_choose(const int4 *__restrict__ cand, const uint32_t *__restrict__ blkN,
+                                                int logS, int segLog, const int32_t *__restrict__ dr,
+                                                const int32_t *__restrict__ segBase, int2 *__restrict__ choice,
+                                                uint32_t *__restrict__ counters)
+{
+    const uint32_t g = blockIdx.x * 256 + threadIdx.x;
+    const uint32_t b = g >> logS, p = g & ((1u << logS) - 1);
+    const uint32_t N = blkN[b];
+    bool bad = false;
+    if (p < N) {
+        const uint32_t n = N - 8;
+        const size_t gb = (size_t)b << logS;
+        const int32_t *drb = dr + gb;
+        const int32_t *sb = segBase + b * KMAX;
+        uint32_t bo = 0, bl = 1;
+        if (p <= n) {
+            const int32_t mine = drb[p] + sb[p >> segLog];
+            int32_t best = 9 * (int32_t)n;  // d[n] = cost[n] + 9n = 9n (ref lib/salz.c:621)
+            if (p < n) {
+                best = drb[p + 1] + sb[(p + 1) >> segLog];
+                if (p >= 1) {  // position 0 is a forced literal
+                    const int4 c = cand[gb + p];
+                    if (c.y >= 3) {
+                        const uint32_t t = p + (uint32_t)c.y;
+                        const int32_t v = drb[t] + sb[t >> segLog] + factor_cost_bits((uint32_t)c.x, (uint32_t)c.y) - 9 * c.y;
+                        if (v < best) { best = v; bo = (uint32_t)c.x; bl = (uint32_t)c.y; }
+                    }
+                    if (c.w >= 3) {
+                        const uint32_t t = p + (uint32_t)c.w;
+                        const int32_t v = drb[t] + sb[t >> segLog] + factor_cost_bits((uint32_t)c.z, (uint32_t)c.w) - 9 * c.w;
+                        if (v < best) { best = v; bo = (uint32_t)c.z; bl = (uint32_t)c.w; }
+                    }
+                }
+            }
+            bad = mine != best;
+        }
+        choice[gb + p] = make_int2((int)bo, (int)bl);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, bad);
+    if (m && (threadIdx.x & 31) == 0) atomicAdd(&counters[9], __popc(m));
 }
 
 // jump[p] = first position >= the end of p's PARSE_CHUNK that the chosen parse
@@ -400,13 +457,14 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     static bool attrSet = false;
     if (!attrSet) {
         cudaFuncSetAttribute(k_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PARSE_SMEM);
+        cudaFuncSetAttribute(k_parse, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         attrSet = true;
     }
-    // Segments per block: enough chains to fill the CTA slots (4 per SM), but a cut
-    // only pays when it is at least 4-fold (two passes + the confirming one).
+    // Segments per block: enough chains to fill the CTA slots, but a cut only pays when
+    // it is at least 4-fold (two passes of the chains + the parallel check).
     int segLog = bd.logS, K = 1;
     {
-        const int slots = ws.numSMs * SALZ_PARSE_CTAS;
+        const int slots = ws.numSMs * SALZ_PARSE_CTAS * NCH;
         int want = ws.parseSegments ? ws.parseSegments : slots / std::max(1, bd.B);
         if (!ws.parseSegments && want < 4) want = 1;
         while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= 16u * PC) { K *= 2; segLog--; }
@@ -420,22 +478,40 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     if (K > 1) {
         if (cudaMemsetAsync(dr, 0, (size_t)bd.B << bd.logS << 2, st) != cudaSuccess) return -1;
     }
-    for (int pass = 0;; pass++) {
-        k_parse<<<dim3(K, bd.B), PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, ws.numSMs, dr, ws.segBase,
-                                                                  ws.segDirty, ws.segChanged, ws.choice);
+    int kLog = 0;
+    while ((1 << kLog) < K) kLog++;
+    const uint32_t chains = (uint32_t)bd.B << kLog;
+    bool chosen = false;
+    const uint32_t chooseGrid = (uint32_t)(((size_t)bd.B << bd.logS) / 256);
+    for (int pass = 1;; pass++) {
+        k_parse<<<(chains + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, kLog, chains,
+                                                                             ws.numSMs, dr, ws.segBase, ws.segDirty,
+                                                                             ws.segChanged);
         lc.launches += 1;
         if (K == 1) break;
-        if (cudaMemsetAsync(ws.counters + 8, 0, 4, st) != cudaSuccess) return -1;
+        if (cudaMemsetAsync(ws.counters + 8, 0, 8, st) != cudaSuccess) return -1;
         k_seg_scan<<<(bd.B + 63) / 64, 64, 0, st>>>(ws.blkN, bd.B, bd.logS, segLog, dr, ws.segBase, ws.segDirty,
                                                     ws.segChanged, ws.counters);
         lc.launches += 1;
-        if (cudaMemcpyAsync(ws.h_counters + 8, ws.counters + 8, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+        // From the second pass on the values are usually final already; checking that in
+        // parallel (k_choose) is much cheaper than a confirming pass of the chains.
+        if (pass >= 2) {
+            k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, dr, ws.segBase, ws.choice,
+                                                 ws.counters);
+            lc.launches += 1;
+        }
+        if (cudaMemcpyAsync(ws.h_counters + 8, ws.counters + 8, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
         if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
-        if (ws.h_counters[8] == 0) break;
+        if (pass >= 2 && ws.h_counters[9] == 0) { chosen = true; break; }
+        if (ws.h_counters[8] == 0) break;  // nothing changed: a fixpoint, k_choose below confirms it
         if (pass > KMAX + 2) {
             fprintf(stderr, "salz_cuda: segmented parse failed to settle\n");
             return -1;
         }
+    }
+    if (!chosen) {
+        k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, dr, ws.segBase, ws.choice, ws.counters);
+        lc.launches += 1;
     }
     k_jump<<<bd.B << (bd.logS - PARSE_CHUNK_LOG), 256, 0, st>>>(ws.blkN, ws.choice, bd.logS, ws.jump);
     lc.launches += 1;
