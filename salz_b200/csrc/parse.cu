@@ -460,14 +460,17 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
         cudaFuncSetAttribute(k_parse, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         attrSet = true;
     }
-    // Segments per block: enough chains to fill the CTA slots, but a cut only pays when
-    // it is at least 4-fold (two passes of the chains + the parallel check).
+    // Segments per block: several chains per slot (NCH chains per CTA, SALZ_PARSE_CTAS CTAs
+    // per SM) so that the slots stay busy to the end of a pass, segments of at least 32768
+    // positions; a cut only pays when it is at least 4-fold (two passes of the chains +
+    // the parallel check against one pass).
     int segLog = bd.logS, K = 1;
     {
         const int slots = ws.numSMs * SALZ_PARSE_CTAS * NCH;
-        int want = ws.parseSegments ? ws.parseSegments : slots / std::max(1, bd.B);
+        int want = ws.parseSegments ? ws.parseSegments : 8 * slots / std::max(1, bd.B);
         if (!ws.parseSegments && want < 4) want = 1;
-        while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= 16u * PC) { K *= 2; segLog--; }
+        const uint32_t minSeg = ws.parseSegments ? 16u * PC : 64u * PC;
+        while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= minSeg) { K *= 2; segLog--; }
     }
     // cost holds d relative to the segment bases: cost[p] = dr[p] + segBase[p >> segLog] - 9p
     // (salz_cuda_debug_stages converts; nothing downstream needs the absolute costs)
