@@ -133,7 +133,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ok = ok && dalloc(c, &ws.cand, M + 64) && dalloc(c, &ws.cost, M + B + 64) && dalloc(c, &ws.choice, M);
     ws.keys[2] = (uint64_t *)ws.cand;  // the candidates are written after the suffix array is complete
     ok = ok && dalloc(c, &ws.jump, M + 64);
-    ok = ok && dalloc(c, &ws.segBase, B * 64) && dalloc(c, &ws.segDirty, B * 64) && dalloc(c, &ws.segChanged, B * 64);
+    ok = ok && dalloc(c, &ws.segBase, B * 64) && dalloc(c, &ws.cost2, M + 64);
     const size_t chunks = M >> PARSE_CHUNK_LOG;
     ok = ok && dalloc(c, &ws.chunkEntry, chunks) && dalloc(c, &ws.chunkTok, chunks) &&
          dalloc(c, &ws.chunkBits, chunks);
@@ -388,7 +388,7 @@ extern "C" int salz_cuda_debug_stages(salz_cuda_ctx *c, const uint8_t *src, size
         // cost[p] (the reference's aux[4p+2]) = d[p] - 9p, d = relative value + segment base
         std::vector<int32_t> ch(2 * n), cs(n + 1), sb(64);
         CKC(c, cudaMemcpy(ch.data(), ws.choice, n * 8, cudaMemcpyDeviceToHost));
-        CKC(c, cudaMemcpy(cs.data(), ws.cost, (n + 1) * 4, cudaMemcpyDeviceToHost));
+        CKC(c, cudaMemcpy(cs.data(), ws.parseDr, (n + 1) * 4, cudaMemcpyDeviceToHost));
         CKC(c, cudaMemcpy(sb.data(), ws.segBase, 64 * 4, cudaMemcpyDeviceToHost));
         for (size_t p = 0; p < n; p++) {
             parse[3 * p] = ch[2 * p];

@@ -64,7 +64,8 @@ constexpr int KMAX = 64;           // segments per block, at most
 constexpr size_t PARSE_SMEM = NCH * (2 * PC * (sizeof(int4) + sizeof(uint32_t)) + (RING + 4) * sizeof(int32_t));
 
 struct SegCtx {
-    const int32_t *dr;     // block's d array, relative per segment
+    const int32_t *dr;     // block's d array of this pass (own segment), relative per segment
+    const int32_t *drOld;  // the previous pass's array (everything right of the segment)
     const int32_t *sbase;  // [K - j] base[m] - base[j] (shared memory)
     uint32_t R;            // first position right of the segment
     uint32_t j;
@@ -74,8 +75,7 @@ struct SegCtx {
 // d[t] relative to this segment's base, t anywhere in the block
 __device__ __forceinline__ int32_t dval(const SegCtx &sg, uint32_t t)
 {
-    const int32_t v = __ldcg(&sg.dr[t]);
-    return (t < sg.R) ? v : v + sg.sbase[(t >> sg.segLog) - sg.j];
+    return (t < sg.R) ? __ldcg(&sg.dr[t]) : __ldcg(&sg.drOld[t]) + sg.sbase[(t >> sg.segLog) - sg.j];
 }
 
 // Consumer record: x = F in d-space, y / z = weight - 9 len of the two ring
@@ -126,27 +126,14 @@ __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const S
 }
 
 // ring -> global d array for chunk c (needed by stage(c-2) and k_choose); ht in [0, HELPERS).
-// Returns true when a value differs from what the array held.
-__device__ __forceinline__ bool flush_chunk(const int32_t *ring, int32_t *drb, uint32_t n, uint32_t c, int ht)
+__device__ __forceinline__ void flush_chunk(const int32_t *ring, int32_t *drb, uint32_t n, uint32_t c, int ht)
 {
-    constexpr int FP = PC / HELPERS;
-    int32_t old[FP];
 #pragma unroll
-    for (int k = 0; k < FP; k++) {
-        const uint32_t p = c * PC + ht + k * HELPERS;
-        old[k] = (p <= n) ? drb[p] : 0;
-    }
-    bool changed = false;
-#pragma unroll
-    for (int k = 0; k < FP; k++) {
+    for (int k = 0; k < PC / HELPERS; k++) {
         const int i = ht + k * HELPERS;
         const uint32_t p = c * PC + i;
-        if (p <= n) {
-            const int32_t v = ring[(c & 1u) * PC + i];
-            if (old[k] != v) { changed = true; drb[p] = v; }
-        }
+        if (p <= n) drb[p] = ring[(c & 1u) * PC + i];
     }
-    return changed;
 }
 __device__ __forceinline__ void helper_barrier(int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(HELPERS) : "memory"); }
 
@@ -166,14 +153,14 @@ __device__ __forceinline__ void sts_i32(uint32_t addr, int32_t v)
 // stream, which is what the SM runs out of first), and every chain has its own
 // HELPERS stager threads, ring and record buffers.  Chain q = b * K + j is segment j of
 // block b; grid = ceil(B * K / NCH).  dr: d values by g, relative per segment;
-// segBase / segChanged / segDirty: [B][KMAX].
+// segBase: [B][KMAX].
 struct Chain {
     uint32_t b, j, N, n, R, cBeg, cEnd;
     bool act, last;
 };
 
 __device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog, int segLog,
-                                          const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ segDirty)
+                                          const uint32_t *__restrict__ blkN)
 {
     Chain ch;
     ch.act = false;
@@ -186,7 +173,6 @@ __device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog,
     ch.n = ch.N - 8;
     const uint32_t L = ch.j << segLog;
     if (L >= ch.N) return ch;
-    if (!segDirty[ch.b * KMAX + ch.j]) return ch;  // nothing to the right changed since this segment was computed
     ch.R = min(ch.N, L + (1u << segLog));
     ch.last = ch.R == ch.N;
     ch.cBeg = L / PC;
@@ -198,16 +184,14 @@ __device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog,
 __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const int4 *__restrict__ cand,
                                                             const uint32_t *__restrict__ blkN, int logS, int segLog,
                                                             int kLog, uint32_t chains, int numSMs, int32_t *dr,
-                                                            const int32_t *__restrict__ segBase,
-                                                            const uint32_t *__restrict__ segDirty,
-                                                            uint32_t *__restrict__ segChanged)
+                                                            const int32_t *drOld,
+                                                            const int32_t *__restrict__ segBase)
 {
     extern __shared__ __align__(16) uint8_t psmem[];
     int4 *stC = (int4 *)psmem;                          // [NCH][2][PC] consumer records
     uint32_t *stD = (uint32_t *)(stC + NCH * 2 * PC);   // [NCH][2][PC] second ring address
     int32_t *rings = (int32_t *)(stD + NCH * 2 * PC);   // [NCH][RING + 4], d-space
     __shared__ int32_t sbase[NCH][KMAX];
-    __shared__ uint32_t s_changed[NCH];
     // co-resident CTAs put their consumer on different warp slots
     const uint32_t lin = blockIdx.x;
     const int cw = (int)((lin + lin / (uint32_t)numSMs) % 4u);
@@ -216,11 +200,11 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
     // the chain this thread works for
     const int ci = (warp == 0) ? lane / (32 / NCH) : (warp - 1) / (HELPERS / 32);
     const int ht = ((warp - 1) % (HELPERS / 32)) * 32 + lane;  // helper thread index inside the chain
-    const Chain ch = chain_of(blockIdx.x * NCH + ci, chains, kLog, segLog, blkN, segDirty);
+    const Chain ch = chain_of(blockIdx.x * NCH + ci, chains, kLog, segLog, blkN);
     uint32_t maxSteps = 0;
 #pragma unroll
     for (int k = 0; k < NCH; k++) {
-        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN, segDirty);
+        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN);
         if (o.act) maxSteps = max(maxSteps, o.cEnd - o.cBeg);
     }
     if (maxSteps == 0) return;
@@ -235,12 +219,11 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
 
     for (int i = threadIdx.x; i < NCH * KMAX; i += PARSE_THREADS) {
         const int k = i / KMAX;
-        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN, segDirty);
+        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN);
         const uint32_t m = o.j + (uint32_t)(i % KMAX);
         sbase[k][i % KMAX] = (o.act && m < KMAX && ((size_t)m << segLog) < o.N)
                                  ? segBase[o.b * KMAX + m] - segBase[o.b * KMAX + o.j] : 0;
     }
-    if (threadIdx.x < NCH) s_changed[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < NCH * (RING + 4); i += PARSE_THREADS) rings[i] = SALZ_INF;
     // lanes of a chain without work idle along with the others: their records must hold loadable addresses
     {
@@ -251,7 +234,7 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
         }
     }
     __syncthreads();
-    SegCtx sg = {drb, sbase[ci], ch.R, ch.j, segLog};
+    SegCtx sg = {drb, drOld + gb, sbase[ci], ch.R, ch.j, segLog};
     const uint32_t nch = ch.act ? ch.cEnd - ch.cBeg : 0;
 
     if (warp >= 1 && ch.act) {
@@ -261,14 +244,13 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
     __syncthreads();
 
     int32_t d = ch.last ? SALZ_INF : 0;  // d[p + 1] relative to the segment's base
-    bool changed = false;
     // step s: the consumer walks chunk cEnd-1-s of every chain that still has one; the
     // stagers flush the chunk it has just left and prepare the one after
     for (uint32_t s = 0; s <= maxSteps; s++) {
         const uint32_t c = ch.cEnd - 1 - min(s, nch ? nch - 1 : 0u);
         if (warp >= 1) {
             if (ch.act && s >= 1 && s <= nch) {
-                changed |= flush_chunk(ring, drb, ch.n, ch.cEnd - s, ht);
+                flush_chunk(ring, drb, ch.n, ch.cEnd - s, ht);
                 helper_barrier(1 + ci);
             }
             if (ch.act && s + 1 < nch)
@@ -320,29 +302,41 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
         }
         __syncthreads();
     }
-    if (warp >= 1 && changed) s_changed[ci] = 1;
-    __syncthreads();
-    if (warp >= 1 && ht == 0 && ch.act) segChanged[ch.b * KMAX + ch.j] = s_changed[ci];
+}
+
+// Heuristic only (the result never depends on it): every 64th position votes whether one of
+// its candidates is longer than `longLen`.  Factors that reach over many segments are what
+// keeps the segmented passes from settling.  counters[10] += votes.
+__global__ void __launch_bounds__(256) k_longcount(const int4 *__restrict__ cand, const uint32_t *__restrict__ blkN,
+                                                   int logS, uint32_t total, int longLen, uint32_t *__restrict__ counters)
+{
+    const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+    bool vote = false;
+    if (i < total) {
+        const uint32_t g = i * 64 + 17;
+        const uint32_t b = g >> logS, p = g & ((1u << logS) - 1);
+        if (p >= 1 && p + 8 < blkN[b]) {
+            const int4 c = cand[g];
+            vote = c.y >= longLen || c.w >= longLen;
+        }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, vote);
+    if (m && (threadIdx.x & 31) == 0) atomicAdd(&counters[10], __popc(m));
 }
 
 // Before the first pass: every base = 9 n_b (the all-literal estimate in d-space,
-// and the exact base of the last segment), every segment dirty.
-__global__ void k_seg_init(const uint32_t *__restrict__ blkN, int B, int32_t *__restrict__ segBase,
-                           uint32_t *__restrict__ segDirty, uint32_t *__restrict__ segChanged)
+// and the exact base of the last segment).
+__global__ void k_seg_init(const uint32_t *__restrict__ blkN, int B, int32_t *__restrict__ segBase)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * KMAX) return;
     segBase[i] = 9 * (int32_t)(blkN[i / KMAX] - 8);
-    segDirty[i] = 1;
-    segChanged[i] = 0;
 }
 
-// After a pass: bases from the d values at the segment starts; a segment is
-// dirty when something to its right changed.  counters[8] += dirty segments.
+// After a pass: bases (absolute d at the segments' right ends) by a suffix sum of the d
+// values at the segment starts.
 __global__ void k_seg_scan(const uint32_t *__restrict__ blkN, int B, int logS, int segLog,
-                           const int32_t *__restrict__ dr, int32_t *__restrict__ segBase,
-                           uint32_t *__restrict__ segDirty, uint32_t *__restrict__ segChanged,
-                           uint32_t *__restrict__ counters)
+                           const int32_t *__restrict__ dr, int32_t *__restrict__ segBase)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -350,16 +344,10 @@ __global__ void k_seg_scan(const uint32_t *__restrict__ blkN, int B, int logS, i
     const int Kb = (int)((N + (1u << segLog) - 1) >> segLog);
     const int32_t *drb = dr + ((size_t)b << logS);
     int32_t base = 9 * (int32_t)(N - 8);
-    uint32_t anyRight = 0, dirty = 0;
     for (int j = Kb - 1; j >= 0; j--) {
         segBase[b * KMAX + j] = base;
-        segDirty[b * KMAX + j] = anyRight;
-        dirty += anyRight;
-        anyRight |= segChanged[b * KMAX + j];
-        segChanged[b * KMAX + j] = 0;
         base += drb[(size_t)j << segLog];  // d at the first position of segment j = base of segment j-1
     }
-    if (dirty) atomicAdd(&counters[8], dirty);
 }
 
 // The choice per position from the d values in global memory, with the reference's
@@ -470,52 +458,66 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
         int want = ws.parseSegments ? ws.parseSegments : 8 * slots / std::max(1, bd.B);
         if (!ws.parseSegments && want < 4) want = 1;
         const uint32_t minSeg = ws.parseSegments ? 16u * PC : 64u * PC;
+        if (!ws.parseSegments && want >= 4) {
+            // inputs with long factors (deep repeats, runs) settle one segment per pass: keep them whole
+            const uint32_t samples = (uint32_t)(((size_t)bd.B << bd.logS) / 64);
+            if (cudaMemsetAsync(ws.counters + 10, 0, 4, st) != cudaSuccess) return -1;
+            k_longcount<<<(samples + 255) / 256, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, samples, 4096, ws.counters);
+            lc.launches += 1;
+            if (cudaMemcpyAsync(ws.h_counters + 10, ws.counters + 10, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+            if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
+            if ((uint64_t)ws.h_counters[10] * 2000 > bd.M / 64) want = 1;
+        }
         while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= minSeg) { K *= 2; segLog--; }
     }
-    // cost holds d relative to the segment bases: cost[p] = dr[p] + segBase[p >> segLog] - 9p
-    // (salz_cuda_debug_stages converts; nothing downstream needs the absolute costs)
-    int32_t *dr = ws.cost;
-    ws.parseSegLog = segLog;
-    k_seg_init<<<(bd.B * KMAX + 255) / 256, 256, 0, st>>>(ws.blkN, bd.B, ws.segBase, ws.segDirty, ws.segChanged);
+    // The d values stay relative to the segment bases: cost[p] = dr[p] + segBase[p >> segLog] - 9p
+    // (salz_cuda_debug_stages converts; nothing downstream needs the absolute costs).
+    // Two arrays: a pass reads what lies right of a segment from the previous pass's array.
+    int32_t *cur = ws.cost, *old = ws.cost2;
+    const uint32_t chooseGrid = (uint32_t)(((size_t)bd.B << bd.logS) / 256);
+    const size_t arrBytes = ((size_t)bd.B << bd.logS) * sizeof(int32_t);
+    bool done = false;
+    k_seg_init<<<(bd.B * KMAX + 255) / 256, 256, 0, st>>>(ws.blkN, bd.B, ws.segBase);
     lc.launches += 1;
     if (K > 1) {
-        if (cudaMemsetAsync(dr, 0, (size_t)bd.B << bd.logS << 2, st) != cudaSuccess) return -1;
-    }
-    int kLog = 0;
-    while ((1 << kLog) < K) kLog++;
-    const uint32_t chains = (uint32_t)bd.B << kLog;
-    bool chosen = false;
-    const uint32_t chooseGrid = (uint32_t)(((size_t)bd.B << bd.logS) / 256);
-    for (int pass = 1;; pass++) {
-        k_parse<<<(chains + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, kLog, chains,
-                                                                             ws.numSMs, dr, ws.segBase, ws.segDirty,
-                                                                             ws.segChanged);
-        lc.launches += 1;
-        if (K == 1) break;
-        if (cudaMemsetAsync(ws.counters + 8, 0, 8, st) != cudaSuccess) return -1;
-        k_seg_scan<<<(bd.B + 63) / 64, 64, 0, st>>>(ws.blkN, bd.B, bd.logS, segLog, dr, ws.segBase, ws.segDirty,
-                                                    ws.segChanged, ws.counters);
-        lc.launches += 1;
-        // From the second pass on the values are usually final already; checking that in
-        // parallel (k_choose) is much cheaper than a confirming pass of the chains.
-        if (pass >= 2) {
-            k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, dr, ws.segBase, ws.choice,
-                                                 ws.counters);
+        int kLog = 0;
+        while ((1 << kLog) < K) kLog++;
+        const uint32_t chains = (uint32_t)bd.B << kLog;
+        if (cudaMemsetAsync(old, 0, arrBytes, st) != cudaSuccess) return -1;  // all-literal estimate: d = base everywhere
+        // Text settles in two passes.  An input that has not after MAX_PASSES (factors reaching over
+        // many segments: one exact segment more per pass) gets the plain one-chain-per-block pass.
+        constexpr int MAX_PASSES = 3;
+        for (int pass = 1; pass <= MAX_PASSES && !done; pass++) {
+            k_parse<<<(chains + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, kLog, chains,
+                                                                                 ws.numSMs, cur, old, ws.segBase);
+            k_seg_scan<<<(bd.B + 63) / 64, 64, 0, st>>>(ws.blkN, bd.B, bd.logS, segLog, cur, ws.segBase);
+            lc.launches += 2;
+            if (pass >= 2) {
+                if (cudaMemsetAsync(ws.counters + 9, 0, 4, st) != cudaSuccess) return -1;
+                k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.counters);
+                lc.launches += 1;
+                if (cudaMemcpyAsync(ws.h_counters + 9, ws.counters + 9, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+                if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
+                done = ws.h_counters[9] == 0;
+                if (!done && ws.h_counters[9] > 16u * (uint32_t)bd.B) break;  // far from settled: no third pass
+            }
+            if (!done) std::swap(cur, old);
+        }
+        if (!done) {
+            segLog = bd.logS;
+            K = 1;
+            k_seg_init<<<(bd.B * KMAX + 255) / 256, 256, 0, st>>>(ws.blkN, bd.B, ws.segBase);
             lc.launches += 1;
         }
-        if (cudaMemcpyAsync(ws.h_counters + 8, ws.counters + 8, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
-        if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
-        if (pass >= 2 && ws.h_counters[9] == 0) { chosen = true; break; }
-        if (ws.h_counters[8] == 0) break;  // nothing changed: a fixpoint, k_choose below confirms it
-        if (pass > KMAX + 2) {
-            fprintf(stderr, "salz_cuda: segmented parse failed to settle\n");
-            return -1;
-        }
     }
-    if (!chosen) {
-        k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, dr, ws.segBase, ws.choice, ws.counters);
-        lc.launches += 1;
+    if (!done) {
+        k_parse<<<(bd.B + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, 0, (uint32_t)bd.B,
+                                                                           ws.numSMs, cur, old, ws.segBase);
+        k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.counters);
+        lc.launches += 2;
     }
+    ws.parseSegLog = segLog;
+    ws.parseDr = cur;
     k_jump<<<bd.B << (bd.logS - PARSE_CHUNK_LOG), 256, 0, st>>>(ws.blkN, ws.choice, bd.logS, ws.jump);
     lc.launches += 1;
     cudaError_t e = cudaGetLastError();

@@ -74,12 +74,13 @@ struct Workspace {
     // candidates / parse
     int4 *cand;        // [Mcap] by g
     int32_t *cost;     // [Mcap + 64] by g: the parse's d values relative to the segment bases (parse.cu)
+    int32_t *cost2;    // [Mcap + 64] the other array of the parse's two (a pass reads the previous pass's values)
+    int32_t *parseDr;  // whichever of cost / cost2 holds the final values of the last parse
     int parseSegLog;   // log2 of the segment length of the last parse
     int parseSegments; // requested segments per block, 0 = automatic
     int2 *choice;      // [Mcap] by g: (offs, len)
     uint32_t *jump;    // [Mcap] by g: first position >= chunk end reached from p 
     int32_t *segBase;  // [Bmax][64] parse segments: d at the segment's right end
-    uint32_t *segDirty, *segChanged;  // [Bmax][64]
     // emit
     uint32_t *chunkEntry; // [Mcap / CHUNK]
     uint32_t *chunkTok;   // [Mcap / CHUNK] tokens starting in chunk -> exclusive prefix
