@@ -222,79 +222,88 @@ def post_bits(l):
     return ((l - 3) >> 3) + 4
 
 
-def parse_model(cand, N, seg_len=256, seed=0):
-    """Model of k_parse / k_seg_scan: the chain in the shifted space d[p] = cost[p] + 9p
-    (one min per position), the block cut into segments of `seg_len` positions that
-    keep d relative to their right end, everything to the right of a segment read as
-    an estimate, passes (segments in arbitrary order, in place) until one changes
-    nothing.  Returns cost[n+1], choice[N,2], jump[N], passes."""
-    import random
-    rnd = random.Random(seed)
+def parse_model(cand, N, seg_len=256, max_passes=3):
+    """Model of parse.cu: the chain in the shifted space d[p] = cost[p] + 9p (one min per
+    position), the block cut into segments of `seg_len` positions that keep d relative to
+    their right end and read everything to their right from the PREVIOUS pass's array
+    (k_parse + k_seg_scan), the parallel check that the recurrence holds everywhere
+    (k_choose) from the second pass on, and after `max_passes` the plain single chain.
+    Returns cost[n+1], choice[N,2], jump[N], passes (0 = fell back to one chain)."""
     n = N - 8
-    K = (N + seg_len - 1) // seg_len
-    dr = np.zeros(N + 1, np.int64)                 # relative d values, in place
-    base = np.full(K, 9 * n, np.int64)             # all-literal estimate; exact for the last segment
-    dirty = [True] * K
-    choice = np.zeros((N, 2), np.int64)
-    choice[:, 1] = 1
-    w = {}                                         # factor weights minus 9 len
+    w = {}
     for p in range(1, n):
         c = cand[p]
         for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))):
             if l >= 3:
                 w[(p, l, o)] = pre_bits(o) + 8 + post_bits(l) - 9 * l
-    passes = 0
-    while any(dirty):
-        passes += 1
-        assert passes <= K + 2, "segmented parse failed to settle"
-        changed = [False] * K
-        order = [j for j in range(K) if dirty[j]]
-        rnd.shuffle(order)
-        for j in order:
-            L, R = j * seg_len, min(N, (j + 1) * seg_len)
 
-            def dval(t):                           # relative to base[j]
-                return dr[t] if t < R else dr[t] + base[t // seg_len] - base[j]
+    def edges(p):
+        c = cand[p]
+        return [(o, l) for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))) if l >= 3]
+
+    def run_pass(seg, old, base):
+        K = (N + seg - 1) // seg
+        new = np.zeros(N + 1, np.int64)
+        for j in range(K):                       # independent CTAs
+            L, R = j * seg, min(N, (j + 1) * seg)
             d = INF if R == N else 0
-            new = {}
             for p in range(R - 1, L - 1, -1):
                 if p > n:
                     continue
                 m = 0 if p == n else INF
                 if 1 <= p < n:
-                    c = cand[p]
-                    for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))):
-                        if l >= 3:
-                            t = p + l
-                            v = new[t] if t < R else dval(t)
-                            m = min(m, v + w[(p, l, o)])
+                    for (o, l) in edges(p):
+                        t = p + l
+                        v = new[t] if t < R else old[t] + base[t // seg] - base[j]
+                        m = min(m, v + w[(p, l, o)])
                 d = min(d, m)
                 new[p] = d
-            for p, v in new.items():
-                if dr[p] != v:
-                    changed[j] = True
-                    dr[p] = v
-            # finisher: the reference's comparisons in its order (literal, PSV, NSV; strict <)
-            for p in range(max(L, 1), min(R, n)):
-                c = cand[p]
-                best, bo, bl = dval(p + 1), 0, 1
-                for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))):
-                    if l >= 3:
-                        v = dval(p + l) + w[(p, l, o)]
+        nb = np.zeros(K, np.int64)               # k_seg_scan
+        b = 9 * n
+        for j in range(K - 1, -1, -1):
+            nb[j] = b
+            b += new[j * seg]
+        return new, nb
+
+    def choose(seg, dr, base):
+        """k_choose: choices + number of positions whose recurrence fails."""
+        choice = np.zeros((N, 2), np.int64)
+        choice[:, 1] = 1
+        bad = 0
+        dabs = lambda t: dr[t] + base[t // seg]
+        for p in range(0, n + 1):
+            best, bo, bl = 9 * n, 0, 1
+            if p < n:
+                best = dabs(p + 1)
+                if p >= 1:
+                    for (o, l) in edges(p):
+                        v = dabs(p + l) + w[(p, l, o)]
                         if v < best:
                             best, bo, bl = v, o, l
-                choice[p] = (bo, bl)
-        # k_seg_scan
-        b = 9 * n
-        any_right = False
-        for j in range(K - 1, -1, -1):
-            base[j] = b
-            dirty[j] = any_right
-            any_right = any_right or changed[j]
-            b += dr[j * seg_len]
-        if K == 1:
-            break
-    cost = np.array([dr[p] + base[p // seg_len] - 9 * p for p in range(n + 1)], np.int64)
+            bad += dabs(p) != best
+            choice[p] = (bo, bl)
+        return choice, bad
+
+    K = (N + seg_len - 1) // seg_len
+    passes, done = 0, False
+    seg = seg_len
+    if K > 1:
+        old = np.zeros(N + 1, np.int64)          # all-literal estimate: d = base everywhere
+        base = np.full(K, 9 * n, np.int64)
+        for passes in range(1, max_passes + 1):
+            dr, base = run_pass(seg, old, base)
+            if passes >= 2:
+                choice, bad = choose(seg, dr, base)
+                if bad == 0:
+                    done = True
+                    break
+            old = dr
+    if not done:
+        passes, seg = 0, 1 << 30
+        dr, base = run_pass(seg, np.zeros(N + 1, np.int64), np.full(1, 9 * n, np.int64))
+        choice, bad = choose(seg, dr, base)
+        assert bad == 0
+    cost = np.array([dr[p] + base[p // seg] - 9 * p for p in range(n + 1)], np.int64)
     jump = np.zeros(N, np.int64)
     for p in range(N - 1, -1, -1):
         end = min(N, ((p >> 11) + 1) << 11)
