@@ -26,6 +26,11 @@ struct salz_cuda_ctx {
     uint32_t *h_salzLen;
     uint64_t *h_outOff;
     cudaEvent_t ev[8];
+    // host-stream pipeline: second copy stream, two text and two output buffers
+    cudaStream_t copyStream;
+    uint8_t *Tbuf[2];
+    uint8_t *outbuf[2];
+    cudaEvent_t tReady[2], oDone[2], computed;
 };
 
 static void set_err(salz_cuda_ctx *c, const char *fmt, ...)
@@ -108,6 +113,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     for (int i = 0; i < 8 && ok; i++) ok = cudaEventCreate(&c->ev[i]) == cudaSuccess;
     ws.Tcap = M + 256;
     ok = ok && dalloc(c, &ws.T, ws.Tcap);
+    c->Tbuf[0] = ws.T;
+    ok = ok && dalloc(c, &c->Tbuf[1], ws.Tcap);
     ok = ok && dalloc(c, &ws.blkN, B);
     const bool packed = 3 * logS <= 64;
     for (int i = 0; i < 2 && ok; i++)
@@ -142,6 +149,13 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
          dalloc(c, &ws.blkOutLen, B) && dalloc(c, &ws.blkOutOff, B + 1);
     ws.outCap = B * ((size_t)ws.S + ws.S / 8 + 16) + 64;
     ok = ok && dalloc(c, &ws.out, ws.outCap);
+    c->outbuf[0] = ws.out;
+    ok = ok && dalloc(c, &c->outbuf[1], ws.outCap);
+    ok = ok && cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; i < 2 && ok; i++)
+        ok = cudaEventCreateWithFlags(&c->tReady[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->oDone[i], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&c->computed, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaMallocHost((void **)&ws.h_counters, 64) == cudaSuccess;
     ok = ok && cudaMallocHost((void **)&c->h_blkN, B * 4) == cudaSuccess;
     ws.h_blkN = c->h_blkN;
@@ -170,6 +184,12 @@ extern "C" void salz_cuda_ctx_destroy(salz_cuda_ctx *c)
     for (int i = 0; i < 8; i++)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
+    if (c->copyStream) cudaStreamDestroy(c->copyStream);
+    for (int i = 0; i < 2; i++) {
+        if (c->tReady[i]) cudaEventDestroy(c->tReady[i]);
+        if (c->oDone[i]) cudaEventDestroy(c->oDone[i]);
+    }
+    if (c->computed) cudaEventDestroy(c->computed);
     delete c;
 }
 
@@ -316,11 +336,82 @@ static int stream_common(salz_cuda_ctx *c, const uint8_t *src, bool srcOnDevice,
     return 0;
 }
 
+// Host buffers: the same loop with the copies on a second stream and two text / output
+// buffers, so that the upload of batch i+1 and the download of batch i-1 run under the
+// kernels of batch i.  A stream that would fit one batch is cut in two for the same reason.
+// (Pageable host memory makes the copies synchronous; the result is the same.)
+static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, size_t block_len, uint8_t *dst,
+                       size_t dst_cap, size_t *dst_len, uint32_t *block_sizes, size_t *nblocks_out)
+{
+    if (!c || !src || !dst || !dst_len || block_len < 9 || src_len == 0) return -1;
+    if (cudaSetDevice(c->device) != cudaSuccess) return -1;
+    Workspace &ws = c->ws;
+    if (block_len > ws.S) { set_err(c, "block_len %zu exceeds context block capacity %u", block_len, ws.S); return -1; }
+    const size_t nblocks = (src_len + block_len - 1) / block_len;
+    const size_t tail = src_len - (nblocks - 1) * block_len;
+    if (tail <= 8) { set_err(c, "last block has %zu bytes (<= 8): not encodable", tail); return -1; }
+    cudaStream_t st = c->stream, cs = c->copyStream;
+    size_t per = ws.Bmax;
+    if (nblocks <= ws.Bmax && nblocks >= 32) per = (nblocks + 1) / 2;
+    const size_t nbatch = (nblocks + per - 1) / per;
+    auto batch_bytes = [&](size_t i) {
+        const size_t off = i * per * block_len;
+        return std::min(src_len - off, per * block_len);
+    };
+    struct Restore {
+        salz_cuda_ctx *c;
+        ~Restore() { c->ws.T = c->Tbuf[0]; c->ws.out = c->outbuf[0]; }
+    } restore{c};
+    // everything queued earlier on the compute stream is done before the buffers are reused
+    CKC(c, cudaEventRecord(c->computed, st));
+    CKC(c, cudaStreamWaitEvent(cs, c->computed, 0));
+    CKC(c, cudaMemcpyAsync(c->Tbuf[0], src, batch_bytes(0), cudaMemcpyHostToDevice, cs));
+    CKC(c, cudaEventRecord(c->tReady[0], cs));
+    size_t outPos = 0;
+    bool outBusy[2] = {false, false};
+    for (size_t i = 0; i < nbatch; i++) {
+        const int k = (int)(i & 1);
+        const size_t b0 = i * per;
+        const int B = (int)std::min(per, nblocks - b0);
+        if (i + 1 < nbatch) {  // Tbuf[k^1] was batch i-1's text: its kernels are complete (run_batch synchronises)
+            CKC(c, cudaMemcpyAsync(c->Tbuf[k ^ 1], src + (i + 1) * per * block_len, batch_bytes(i + 1),
+                                   cudaMemcpyHostToDevice, cs));
+            CKC(c, cudaEventRecord(c->tReady[k ^ 1], cs));
+        }
+        for (int b = 0; b < B; b++)
+            c->h_blkN[b] = (uint32_t)std::min(block_len, src_len - (b0 + b) * block_len);
+        CKC(c, cudaStreamWaitEvent(st, c->tReady[k], 0));
+        if (outBusy[k]) CKC(c, cudaStreamWaitEvent(st, c->oDone[k], 0));  // batch i-2's records have left outbuf[k]
+        ws.T = c->Tbuf[k];
+        ws.out = c->outbuf[k];
+        if (run_batch(c, B, block_len, 1, 5)) return -1;
+        for (int b = 0; b < B; b++) {
+            size_t N = c->h_blkN[b];
+            if (c->h_salzLen[b] > 4 + N + (N + 63) / 64 * 8) {
+                set_err(c, "block %zu: intermediate stream exceeds salz_encoded_len_max (reference fails too)", b0 + b);
+                return -1;
+            }
+        }
+        const size_t produced = (size_t)c->h_outOff[B];
+        if (outPos + produced > dst_cap) { set_err(c, "output buffer too small"); return -1; }
+        CKC(c, cudaMemcpyAsync(dst + outPos, c->outbuf[k], produced, cudaMemcpyDeviceToHost, cs));  // kernels are complete
+        CKC(c, cudaEventRecord(c->oDone[k], cs));
+        outBusy[k] = true;
+        if (block_sizes)
+            for (int b = 0; b < B; b++) block_sizes[b0 + b] = c->h_outLen[b];
+        outPos += produced;
+    }
+    CKC(c, cudaStreamSynchronize(cs));
+    *dst_len = outPos;
+    if (nblocks_out) *nblocks_out = nblocks;
+    return 0;
+}
+
 extern "C" int salz_cuda_encode_stream(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, size_t block_len,
                                        uint8_t *dst, size_t dst_cap, size_t *dst_len, uint32_t *block_sizes,
                                        size_t *nblocks)
 {
-    return stream_common(c, src, false, src_len, block_len, dst, false, dst_cap, dst_len, block_sizes, nblocks);
+    return stream_host(c, src, src_len, block_len, dst, dst_cap, dst_len, block_sizes, nblocks);
 }
 
 extern "C" int salz_cuda_encode_stream_device(salz_cuda_ctx *c, const uint8_t *d_src, size_t src_len,

@@ -180,6 +180,47 @@ def test_batched_stream_matches_per_block_oracle(enc, orc):
     assert stream == want
 
 
+def test_pipelined_host_stream_paths(orc):
+    """salz_cuda_encode_stream with host buffers overlaps copies and kernels (two text and
+    two output buffers): a stream that fits one batch is cut in two, a longer one runs
+    batch after batch; pinned and pageable memory; the device-resident entry on the same
+    context afterwards.  All must give the per-block reference records."""
+    import torch
+    bl = 1 << 16
+    e = salz_b200.SalzCuda(0, bl, 48)
+    try:
+        data = np.concatenate([synth.english_like(70 * bl, seed=31), synth.uniform_random(5 * bl, seed=32),
+                               synth.dna_like(60 * bl + 4321, seed=33, block=bl)])   # 136 blocks: 3 batches of 48
+        want = b""
+        for off in range(0, len(data), bl):
+            blk = orc.encode(data[off: off + bl])
+            want += len(blk).to_bytes(4, "little") + blk
+        stream, sizes = e.encode_stream(data, bl)
+        assert stream == want
+        short = data[: 40 * bl + 999]                                            # 41 blocks: one batch, cut in two
+        nrec = 0
+        pos = 0
+        for _ in range(41):
+            ln = int.from_bytes(want[pos: pos + 4], "little")
+            pos += 4 + ln
+            nrec += 1
+            if nrec == 40:
+                break
+        stream2, sizes2 = e.encode_stream(short, bl)
+        assert stream2[:pos] == want[:pos] and len(sizes2) == 41
+        # pinned source and destination through the pointer entry
+        src = torch.from_numpy(data.copy()).pin_memory()
+        cap = salz_b200.api.stream_len_max(len(data), bl)
+        dst = torch.empty(cap, dtype=torch.uint8).pin_memory()
+        n = e.encode_stream_ptr(src.data_ptr(), len(data), bl, dst.data_ptr(), cap)
+        n = n[0] if isinstance(n, tuple) else n
+        assert bytes(dst[:n].numpy()) == want
+        # the other entries still work on the same context (buffers restored)
+        assert e.encode(data[:bl]) == orc.encode(data[:bl])
+    finally:
+        e.close()
+
+
 def test_stream_rejects_tiny_tail(enc):
     bl = 1 << 15
     with pytest.raises(salz_b200.SalzCudaError):
