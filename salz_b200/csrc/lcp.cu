@@ -36,7 +36,7 @@ __device__ __forceinline__ uint32_t lcp_private(const uint8_t *Ta, const uint8_t
     return lim;
 }
 
-__global__ void __launch_bounds__(LT) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
+__global__ void __launch_bounds__(LT, 2) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
                                                          const uint32_t *__restrict__ blkN,
                                                          const uint64_t *__restrict__ rank,
                                                          const uint32_t *__restrict__ SA, int logS,
