@@ -68,6 +68,7 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     }
     const size_t gb = (size_t)b << logS;
     int2 *cd = cand2 + 2 * gb;
+    int4 *cd4 = (int4 *)cd;
 
     for (int j = tid; j < ATS; j += AT) {
         const uint32_t r = t0 + j;
@@ -90,15 +91,21 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
             int32_t acc = sm[sb + i];
             lmin = min(lmin, acc);
             while (top >= 0 && topVal > v) {       // i is the NSV of top
-                cd[2 * topVal + 1] = make_int2(topVal - v, acc);
-                acc = min(acc, sm[sb + top]);
                 const uint32_t lk = sv[sb + top] & 0xffu;
-                top = (lk & LINK_PM) ? -1 : (int)lk;
-                if (top >= 0) topVal = (int32_t)(sv[sb + top] >> 8);
+                const int32_t tm = sm[sb + top];   // min LCP over (PSV of top, top]
+                if (lk & LINK_PM) {                // its PSV lies outside the segment: NSV half only
+                    cd[2 * topVal + 1] = make_int2(topVal - v, acc);
+                    top = -1;
+                } else {                           // both known: one 16-byte store instead of two 8-byte ones
+                    const int32_t pv = (int32_t)(sv[sb + (int)lk] >> 8);
+                    cd4[topVal] = make_int4(topVal - pv, tm, topVal - v, acc);
+                    top = (int)lk;
+                    topVal = pv;
+                }
+                acc = min(acc, tm);
             }
             sm[sb + i] = acc;
-            if (top >= 0) {                        // top is the PSV of i
-                cd[2 * v] = make_int2(v - topVal, acc);
+            if (top >= 0) {                        // top is the PSV of i: written when i leaves the stack
                 sv[sb + i] = ((uint32_t)v << 8) | (uint32_t)top;
             } else {                               // prefix minimum: PSV lies further left
                 sv[sb + i] = ((uint32_t)v << 8) | LINK_PM | LINK_NONE;
@@ -195,13 +202,20 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
                     acc = min(acc, segLcp[s]);
                 }
             }
+            // what is still on the stack has not had its in-segment PSV written yet
+            const bool havePsv = !(w & LINK_PM);
+            const int2 ps = havePsv ? make_int2(v - (int32_t)(sv[sb + (int)(w & 0x7fu)] >> 8), sm[sb + e]) : make_int2(0, 0);
             if (s < AT) {
                 int f = s * APAD;                  // first prefix minimum of that segment
                 while ((int32_t)(sv[f] >> 8) > v) f = s * APAD + (int)(sv[f] & 0x7fu);
-                cd[2 * v + 1] = make_int2(v - (int32_t)(sv[f] >> 8), min(acc, sm[f]));
+                const int2 ns = make_int2(v - (int32_t)(sv[f] >> 8), min(acc, sm[f]));
+                if (havePsv) cd4[v] = make_int4(ps.x, ps.y, ns.x, ns.y);
+                else cd[2 * v + 1] = ns;
             } else if (lastTile) {
-                cd[2 * v + 1] = make_int2(v + 1, 0);
+                if (havePsv) cd4[v] = make_int4(ps.x, ps.y, v + 1, 0);
+                else cd[2 * v + 1] = make_int2(v + 1, 0);
             } else {
+                if (havePsv) cd[2 * v] = ps;
                 farItems[atomicAdd(farCount, 1u)] = far_item((uint32_t)gb + t0 + tid * AL + e, 1, acc);
             }
             accR = min(accR, sm[sb + e]);

@@ -822,7 +822,10 @@ __device__ __forceinline__ void sort_network(uint64_t (&k)[N])
 
 struct HK3 { uint32_t head, pst, keep; };  // head/pst: window index + 1 of the last flagged element (0 none)
 
-__global__ void __launch_bounds__(LT, 3) k_local(const uint64_t *__restrict__ keysIn, ListView lv,
+#ifndef SALZ_LCTAS
+#define SALZ_LCTAS 3
+#endif
+__global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__restrict__ keysIn, ListView lv,
                                               const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ h0,
                                               int logS, uint32_t round, int passes, uint64_t *__restrict__ rank,
                                               uint32_t *__restrict__ SA, uint64_t *__restrict__ outS,
