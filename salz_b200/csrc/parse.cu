@@ -40,17 +40,20 @@ namespace {
 // K = 1 is the plain single pass (nothing is estimated).
 // ---------------------------------------------------------------------------
 #ifndef SALZ_PC
-#define SALZ_PC 512
+#define SALZ_PC 256
 #endif
 #ifndef SALZ_HELPERS
-#define SALZ_HELPERS 64
+#define SALZ_HELPERS 32
 #endif
 #ifndef SALZ_PARSE_CTAS
-#define SALZ_PARSE_CTAS 2
+#define SALZ_PARSE_CTAS 4
 #endif
 constexpr int PC = SALZ_PC;        // positions per staged chunk (long enough to hide the helpers' memory latency)
 constexpr int HELPERS = SALZ_HELPERS;  // stager threads
-constexpr int PER = 8;             // positions a helper thread has in flight
+#ifndef SALZ_PER
+#define SALZ_PER 8
+#endif
+constexpr int PER = SALZ_PER;             // positions a helper thread has in flight
 constexpr int SUBS = PC / (HELPERS * PER);  // batches of PER positions per helper thread and chunk
 #ifndef SALZ_NCH
 #define SALZ_NCH 4
@@ -61,7 +64,7 @@ constexpr int PARSE_THREADS = 32 * PARSE_WARPS;  // consumer warp + stagers of e
 constexpr int NOT_FAR = -1;
 constexpr int RING = 2 * PC;       // ring entries; entry RING is a constant INF (absent edge)
 constexpr int KMAX = 64;           // segments per block, at most
-constexpr size_t PARSE_SMEM = NCH * (2 * PC * (sizeof(int4) + sizeof(uint32_t)) + (RING + 4) * sizeof(int32_t));
+constexpr size_t PARSE_SMEM = NCH * (2 * PC * sizeof(int4) + (RING + 4) * sizeof(int32_t));
 
 struct SegCtx {
     const int32_t *dr;     // block's d array of this pass (own segment), relative per segment
@@ -79,16 +82,15 @@ __device__ __forceinline__ int32_t dval(const SegCtx &sg, uint32_t t)
 }
 
 // Consumer record: x = F in d-space, y / z = weight - 9 len of the two ring
-// edges, w and sd[] = shared-memory addresses of their ring entries.
+// edges, w = byte offsets of their ring entries (low / high 16 bits).
 __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const SegCtx &sg, uint32_t n,
-                                            uint32_t chunk, int4 *sc, uint32_t *sd, uint32_t ringAddr, int tid)
+                                            uint32_t chunk, int4 *sc, int tid)
 {
     const uint32_t farFrom = min((chunk + 2) * PC, sg.R);  // targets >= this are read from global memory
 #pragma unroll 1
   for (int sub = 0; sub < SUBS; sub++) {
     const uint32_t base = chunk * PC + sub * (HELPERS * PER);
     sc += (sub ? HELPERS * PER : 0);
-    sd += (sub ? HELPERS * PER : 0);
     int4 c[PER];
 #pragma unroll
     for (int k = 0; k < PER; k++) {
@@ -119,8 +121,7 @@ __device__ __forceinline__ void stage_chunk(const int4 *__restrict__ cd, const S
             if (p + (uint32_t)c[k].w >= farFrom) F = min(F, w + t2[k]);
             else { w2 = w; o2 = ((p + (uint32_t)c[k].w) & (RING - 1)) * 4; }
         }
-        sc[tid + k * HELPERS] = make_int4(F, w1, w2, (int)(ringAddr + o1));
-        sd[tid + k * HELPERS] = ringAddr + o2;
+        sc[tid + k * HELPERS] = make_int4(F, w1, w2, (int)(o1 | (o2 << 16)));
     }
   }
 }
@@ -189,8 +190,7 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
 {
     extern __shared__ __align__(16) uint8_t psmem[];
     int4 *stC = (int4 *)psmem;                          // [NCH][2][PC] consumer records
-    uint32_t *stD = (uint32_t *)(stC + NCH * 2 * PC);   // [NCH][2][PC] second ring address
-    int32_t *rings = (int32_t *)(stD + NCH * 2 * PC);   // [NCH][RING + 4], d-space
+    int32_t *rings = (int32_t *)(stC + NCH * 2 * PC);   // [NCH][RING + 4], d-space
     __shared__ int32_t sbase[NCH][KMAX];
     // co-resident CTAs put their consumer on different warp slots
     const uint32_t lin = blockIdx.x;
@@ -214,7 +214,6 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
     int32_t *drb = dr + gb;
     int32_t *ring = rings + ci * (RING + 4);
     int4 *myC = stC + ci * 2 * PC;
-    uint32_t *myD = stD + ci * 2 * PC;
     const uint32_t ringAddr = (uint32_t)__cvta_generic_to_shared(ring);
 
     for (int i = threadIdx.x; i < NCH * KMAX; i += PARSE_THREADS) {
@@ -227,10 +226,8 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
     for (int i = threadIdx.x; i < NCH * (RING + 4); i += PARSE_THREADS) rings[i] = SALZ_INF;
     // lanes of a chain without work idle along with the others: their records must hold loadable addresses
     {
-        const uint32_t anyRing = (uint32_t)__cvta_generic_to_shared(rings);
         for (int i = threadIdx.x; i < NCH * 2 * PC; i += PARSE_THREADS) {
-            stC[i] = make_int4(SALZ_INF, 0, 0, (int)anyRing);
-            stD[i] = anyRing;
+            stC[i] = make_int4(SALZ_INF, 0, 0, 0);
         }
     }
     __syncthreads();
@@ -239,7 +236,7 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
 
     if (warp >= 1 && ch.act) {
         const uint32_t c = ch.cEnd - 1;
-        stage_chunk(cd, sg, ch.n, c, myC + (c & 1) * PC, myD + (c & 1) * PC, ringAddr, ht);
+        stage_chunk(cd, sg, ch.n, c, myC + (c & 1) * PC, ht);
     }
     __syncthreads();
 
@@ -254,36 +251,31 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
                 helper_barrier(1 + ci);
             }
             if (ch.act && s + 1 < nch)
-                stage_chunk(cd, sg, ch.n, c - 1, myC + ((c - 1) & 1) * PC, myD + ((c - 1) & 1) * PC, ringAddr, ht);
+                stage_chunk(cd, sg, ch.n, c - 1, myC + ((c - 1) & 1) * PC, ht);
         } else {
             const bool live = s < nch;
             if (__any_sync(0xffffffffu, live)) {
                 const int4 *rc = myC + (c & 1) * PC;
-                const uint32_t *rd = myD + (c & 1) * PC;
                 // ring slot of position c*PC + i is ((c & 1) * PC + i)
                 const uint32_t slot0 = ringAddr + (c & 1u) * PC * 4;
                 int4 r0 = rc[PC - 1], r1 = rc[PC - 2];
-                int32_t a0 = lds_i32((uint32_t)r0.w), b0 = lds_i32(rd[PC - 1]);
-                int32_t a1 = lds_i32((uint32_t)r1.w), b1 = lds_i32(rd[PC - 2]);
+                int32_t a0 = lds_i32(ringAddr + ((uint32_t)r0.w & 0xffffu)), b0 = lds_i32(ringAddr + ((uint32_t)r0.w >> 16));
+                int32_t a1 = lds_i32(ringAddr + ((uint32_t)r1.w & 0xffffu)), b1 = lds_i32(ringAddr + ((uint32_t)r1.w >> 16));
                 // Records of positions i-2 .. i-2-HB+1 are fetched one half-body ahead of their
                 // use; the ring loads of position j-2 go out before position j is finished (its
                 // targets are >= j+1: all stored).
                 constexpr int HB = 4;
                 int4 X[HB], Y[HB];
-                uint32_t XD[HB], YD[HB];
 #pragma unroll
-                for (int k = 0; k < HB; k++) { X[k] = rc[(PC - 3 - k) & (PC - 1)]; XD[k] = rd[(PC - 3 - k) & (PC - 1)]; }
-                auto half = [&](int4 (&use)[HB], uint32_t (&useD)[HB], int4 (&load)[HB], uint32_t (&loadD)[HB], int i) {
+                for (int k = 0; k < HB; k++) X[k] = rc[(PC - 3 - k) & (PC - 1)];
+                auto half = [&](int4 (&use)[HB], int4 (&load)[HB], int i) {
 #pragma unroll
-                    for (int k = 0; k < HB; k++) {
-                        load[k] = rc[(i - k - 2 - HB) & (PC - 1)];
-                        loadD[k] = rd[(i - k - 2 - HB) & (PC - 1)];
-                    }
+                    for (int k = 0; k < HB; k++) load[k] = rc[(i - k - 2 - HB) & (PC - 1)];
 #pragma unroll
                     for (int k = 0; k < HB; k++) {
                         const int4 r2 = use[k];
-                        const int32_t a2 = lds_i32((uint32_t)r2.w);
-                        const int32_t b2 = lds_i32(useD[k]);
+                        const int32_t a2 = lds_i32(ringAddr + ((uint32_t)r2.w & 0xffffu));
+                        const int32_t b2 = lds_i32(ringAddr + ((uint32_t)r2.w >> 16));
                         const int32_t nd = min(d, min(r0.x, min(a0 + r0.y, b0 + r0.z)));
                         if (live) {  // a finished chain's lanes idle along (records may be stale)
                             d = nd;
@@ -295,8 +287,8 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
                 };
 #pragma unroll 1
                 for (int i = PC - 1; i >= 0; i -= 2 * HB) {
-                    half(X, XD, Y, YD, i);
-                    half(Y, YD, X, XD, i - HB);
+                    half(X, Y, i);
+                    half(Y, X, i - HB);
                 }
             }
         }
@@ -449,8 +441,8 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
         attrSet = true;
     }
     // Segments per block: several chains per slot (NCH chains per CTA, SALZ_PARSE_CTAS CTAs
-    // per SM) so that the slots stay busy to the end of a pass, segments of at least 32768
-    // positions; a cut only pays when it is at least 4-fold (two passes of the chains +
+    // per SM) so that the slots stay busy to the end of a pass, segments of at least 64 chunks (16384)
+    // positions); a cut only pays when it is at least 4-fold (two passes of the chains +
     // the parallel check against one pass).
     int segLog = bd.logS, K = 1;
     {
