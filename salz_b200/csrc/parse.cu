@@ -53,7 +53,7 @@ constexpr int HELPERS = SALZ_HELPERS;  // stager threads
 #ifndef SALZ_PER
 #define SALZ_PER 8
 #endif
-constexpr int PER = SALZ_PER;             // positions a helper thread has in flight
+constexpr int PER = SALZ_PER;  // positions a helper thread has in flight
 constexpr int SUBS = PC / (HELPERS * PER);  // batches of PER positions per helper thread and chunk
 #ifndef SALZ_NCH
 #define SALZ_NCH 4

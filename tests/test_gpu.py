@@ -219,6 +219,14 @@ def test_pipelined_host_stream_paths(orc):
         assert e.encode(data[:bl]) == orc.encode(data[:bl])
     finally:
         e.close()
+    # other batch capacities: one batch cut in two (68 + 68) / two full batches (ragged last block)
+    for bmax in (160, 68):
+        e = salz_b200.SalzCuda(0, bl, bmax)
+        try:
+            stream, sizes = e.encode_stream(data, bl)
+            assert stream == want and len(sizes) == 136
+        finally:
+            e.close()
 
 
 def test_stream_rejects_tiny_tail(enc):
