@@ -36,15 +36,21 @@ __device__ __forceinline__ uint32_t lcp_private(const uint8_t *Ta, const uint8_t
     return lim;
 }
 
-__global__ void __launch_bounds__(LT, 2) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
+// One thread per position, CTAs of IT threads (a tile of LT positions is IT/LT CTAs: a
+// CTA is gone as soon as its own warps are, and the tile maximum is an atomicMax per warp;
+// tileMax is zeroed before the launch).
+constexpr int IT = 256;
+#ifndef SALZ_PLCP_CTAS
+#define SALZ_PLCP_CTAS 6
+#endif
+__global__ void __launch_bounds__(IT, SALZ_PLCP_CTAS) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
                                                          const uint32_t *__restrict__ blkN,
                                                          const uint64_t *__restrict__ rank,
                                                          const uint32_t *__restrict__ SA, int logS,
                                                          int32_t *__restrict__ V, int32_t *__restrict__ tileMax)
 {
-    __shared__ int32_t wmax[LT / 32];
     const uint32_t Smask = (1u << logS) - 1;
-    const uint32_t g = blockIdx.x * LT + threadIdx.x;
+    const uint32_t g = blockIdx.x * IT + threadIdx.x;
     const uint32_t b = g >> logS, p = g & Smask;
     const uint32_t n = blkN[b] - 8;  // blkN >= 9 for every block of a batch
     const uint8_t *Tb = T + (size_t)b * Tstride;
@@ -59,12 +65,27 @@ __global__ void __launch_bounds__(LT, 2) k_plcp_irreducible(const uint8_t *__res
             v = (int32_t)p;  // smallest suffix of the block: PLCP = 0
         } else {
             q = SA[r - 1];
-            bool irreducible = (p == 0) || (q == 0) || (Tb[p - 1] != Tb[q - 1]);
-            if (irreducible) {
-                cap = n - max(p, q);
+            cap = n - max(p, q);
+            if (p == 0 || q == 0) {
                 l = lcp_private(Tb + p, Tb + q, cap, 32);
                 pending = (l == 32 && cap > 32);
                 v = (int32_t)(l + p);
+            } else {
+                // one load per side: the preceding byte (irreducible if it differs) and
+                // the first 7 bytes of the comparison
+                const uint64_t x = load_u64_unaligned(Tb + p - 1) ^ load_u64_unaligned(Tb + q - 1);
+                if (x & 0xffu) {
+                    const uint64_t y = x >> 8;
+                    if (y) {
+                        l = min((uint32_t)(__ffsll((long long)y) - 1) >> 3, cap);
+                    } else {
+                        l = 7;
+                        if (cap > 7) l += lcp_private(Tb + p + 7, Tb + q + 7, cap - 7, 32);
+                        else l = cap;
+                        pending = (l == 39 && cap > 39);
+                    }
+                    v = (int32_t)(l + p);
+                }
             }
         }
     }
@@ -76,7 +97,7 @@ __global__ void __launch_bounds__(LT, 2) k_plcp_irreducible(const uint8_t *__res
         uint32_t p0 = __shfl_sync(0xffffffffu, p, src);
         uint32_t q0 = __shfl_sync(0xffffffffu, q, src);
         uint32_t cap0 = __shfl_sync(0xffffffffu, cap, src);
-        uint32_t l0 = 32;
+        uint32_t l0 = __shfl_sync(0xffffffffu, l, src);
         for (;;) {
             uint32_t off = l0 + lane * 16;
             uint32_t mine = 16;  // matching bytes in my 16-byte window
@@ -109,14 +130,7 @@ __global__ void __launch_bounds__(LT, 2) k_plcp_irreducible(const uint8_t *__res
     int32_t mx = v;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) wmax[threadIdx.x >> 5] = mx;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        int32_t w = wmax[threadIdx.x];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) w = max(w, __shfl_xor_sync(0xffffffffu, w, o));
-        if (threadIdx.x == 0) tileMax[blockIdx.x] = w;
-    }
+    if (lane == 0 && mx > 0) atomicMax(&tileMax[g / LT], mx);
 }
 
 // One CTA per block: exclusive max-scan of the tile maxima, in place.
@@ -147,7 +161,8 @@ __global__ void __launch_bounds__(256) k_plcp_scan_tiles(int32_t *__restrict__ t
     }
 }
 
-// PLCP[g] = inclusive-max(V)[g] - p, also scattered to LCP[ISA[g]].
+// PLCP[g] = inclusive-max(V)[g] - p, also scattered to LCP[ISA[g]] (gathering
+// LCP[i] = PLCP[SA[i]] in k_pyramid_l1 instead measured the same).
 __global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ blkN,
                                                    const uint64_t *__restrict__ rank, int logS,
                                                    const int32_t *__restrict__ tileMax, int32_t *__restrict__ V,
@@ -237,7 +252,8 @@ int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter
     const size_t total = (size_t)bd.B * bd.S;  // padded index space of this batch
     const uint32_t tiles = (uint32_t)(total / LT);
     const uint32_t tilesPerBlock = bd.S / LT;
-    k_plcp_irreducible<<<tiles, LT, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.rank, ws.SA, bd.logS, ws.plcp,
+    if (cudaMemsetAsync(ws.tileMax, 0, (size_t)tiles * sizeof(int32_t), st) != cudaSuccess) return -1;
+    k_plcp_irreducible<<<tiles * (LT / IT), IT, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.rank, ws.SA, bd.logS, ws.plcp,
                                              ws.tileMax);
     k_plcp_scan_tiles<<<bd.B, 256, 0, st>>>(ws.tileMax, tilesPerBlock);
     k_plcp_apply<<<tiles, LT, 0, st>>>(ws.blkN, ws.rank, bd.logS, ws.tileMax, ws.plcp, ws.lcp);
