@@ -137,8 +137,10 @@ void salz_cuda_set_sort_mode(salz_cuda_ctx *ctx, int mode);
  * optimize_factorization, lib/salz.c:610-662, is one serial loop per block).
  * 0 (default) = automatic: enough chains to fill the GPU when the batch has few
  * blocks, one chain per block otherwise; k >= 1 = at most k segments (rounded
- * down to a power of two, segments never shorter than 16384 positions).  The
- * parse is exact for every k (the passes repeat until nothing changes). */
+ * down to a power of two, segments never shorter than 4096 positions); k <= -1
+ * = |k| segments with the shortened first pass forced (automatic mode decides
+ * that by itself).  The parse is exact for every k: a parallel check of the
+ * recurrence at every position decides whether another pass is needed. */
 void salz_cuda_set_parse_segments(salz_cuda_ctx *ctx, int k);
 
 /* Run this context's copies and kernels on the caller's CUDA stream

@@ -126,7 +126,7 @@ class SalzCuda:
         self.lib.salz_cuda_set_sort_mode(self.ctx, mode)
 
     def set_parse_segments(self, k):
-        """Segments per block of the parse: 0 = automatic, k >= 1 = at most k."""
+        """Segments per block of the parse: 0 = automatic, k >= 1 = at most k, k <= -1 = |k| with the shortened first pass."""
         self.lib.salz_cuda_set_parse_segments(self.ctx, k)
 
     def set_stream(self, cuda_stream):

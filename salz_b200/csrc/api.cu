@@ -93,7 +93,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
 
     Workspace &ws = c->ws;
     memset(&ws, 0, sizeof(ws));
-    ws.parseSegments = ps ? std::max(0, atoi(ps)) : 0;
+    ws.parseSegments = ps ? atoi(ps) : 0;
     cudaDeviceGetAttribute(&ws.numSMs, cudaDevAttrMultiProcessorCount, device);
     if (ws.numSMs <= 0) ws.numSMs = 148;
     int logS = 12;
@@ -203,7 +203,7 @@ extern "C" void salz_cuda_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 extern "C" const char *salz_cuda_last_error(const salz_cuda_ctx *c) { return c ? c->err : "no context"; }
 extern "C" void salz_cuda_set_sort_mode(salz_cuda_ctx *c, int mode) { if (c) c->sortMode = mode ? 1 : 0; }
-extern "C" void salz_cuda_set_parse_segments(salz_cuda_ctx *c, int k) { if (c) c->ws.parseSegments = k > 0 ? k : 0; }
+extern "C" void salz_cuda_set_parse_segments(salz_cuda_ctx *c, int k) { if (c) c->ws.parseSegments = k; }
 extern "C" void salz_cuda_set_stream(salz_cuda_ctx *c, void *stream)
 {
     if (!c) return;

@@ -37,7 +37,9 @@ namespace {
 // is the reference's.  Pass i leaves at least the i rightmost segments exact (at
 // most K+1 passes); text-like inputs are exact after two because only relative
 // costs matter and the optimal paths of neighbouring positions merge quickly.
-// K = 1 is the plain single pass (nothing is estimated).
+// K = 1 is the plain single pass (nothing is estimated).  The first of the passes
+// only has to supply the left end of every segment to the second one, so it walks
+// just WARM_CHUNKS chunks per segment (see parse_build).
 // ---------------------------------------------------------------------------
 #ifndef SALZ_PC
 #define SALZ_PC 256
@@ -64,6 +66,10 @@ constexpr int PARSE_THREADS = 32 * PARSE_WARPS;  // consumer warp + stagers of e
 constexpr int NOT_FAR = -1;
 constexpr int RING = 2 * PC;       // ring entries; entry RING is a constant INF (absent edge)
 constexpr int KMAX = 64;           // segments per block, at most
+#ifndef SALZ_WARM
+#define SALZ_WARM 8
+#endif
+constexpr uint32_t WARM_CHUNKS = SALZ_WARM;  // chunks per segment the warm-up pass walks (0: a full first pass)
 constexpr size_t PARSE_SMEM = NCH * (2 * PC * sizeof(int4) + (RING + 4) * sizeof(int32_t));
 
 struct SegCtx {
@@ -160,7 +166,8 @@ struct Chain {
     bool act, last;
 };
 
-__device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog, int segLog,
+// warm > 0: only the leftmost `warm` chunks of the segment (the warm-up pass).
+__device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog, int segLog, uint32_t warm,
                                           const uint32_t *__restrict__ blkN)
 {
     Chain ch;
@@ -174,7 +181,7 @@ __device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog,
     ch.n = ch.N - 8;
     const uint32_t L = ch.j << segLog;
     if (L >= ch.N) return ch;
-    ch.R = min(ch.N, L + (1u << segLog));
+    ch.R = min(ch.N, L + (warm ? min(1u << segLog, warm * PC) : (1u << segLog)));
     ch.last = ch.R == ch.N;
     ch.cBeg = L / PC;
     ch.cEnd = (ch.R + PC - 1) / PC;  // segment lengths are multiples of PC
@@ -184,7 +191,7 @@ __device__ __forceinline__ Chain chain_of(uint32_t q, uint32_t chains, int kLog,
 
 __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const int4 *__restrict__ cand,
                                                             const uint32_t *__restrict__ blkN, int logS, int segLog,
-                                                            int kLog, uint32_t chains, int numSMs, int32_t *dr,
+                                                            int kLog, uint32_t chains, uint32_t warm, int numSMs, int32_t *dr,
                                                             const int32_t *drOld,
                                                             const int32_t *__restrict__ segBase)
 {
@@ -200,11 +207,11 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
     // the chain this thread works for
     const int ci = (warp == 0) ? lane / (32 / NCH) : (warp - 1) / (HELPERS / 32);
     const int ht = ((warp - 1) % (HELPERS / 32)) * 32 + lane;  // helper thread index inside the chain
-    const Chain ch = chain_of(blockIdx.x * NCH + ci, chains, kLog, segLog, blkN);
+    const Chain ch = chain_of(blockIdx.x * NCH + ci, chains, kLog, segLog, warm, blkN);
     uint32_t maxSteps = 0;
 #pragma unroll
     for (int k = 0; k < NCH; k++) {
-        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN);
+        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, warm, blkN);
         if (o.act) maxSteps = max(maxSteps, o.cEnd - o.cBeg);
     }
     if (maxSteps == 0) return;
@@ -218,7 +225,7 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
 
     for (int i = threadIdx.x; i < NCH * KMAX; i += PARSE_THREADS) {
         const int k = i / KMAX;
-        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, blkN);
+        const Chain o = chain_of(blockIdx.x * NCH + k, chains, kLog, segLog, warm, blkN);
         const uint32_t m = o.j + (uint32_t)(i % KMAX);
         sbase[k][i % KMAX] = (o.act && m < KMAX && ((size_t)m << segLog) < o.N)
                                  ? segBase[o.b * KMAX + m] - segBase[o.b * KMAX + o.j] : 0;
@@ -298,22 +305,26 @@ __global__ void __launch_bounds__(PARSE_THREADS, SALZ_PARSE_CTAS) k_parse(const 
 
 // Heuristic only (the result never depends on it): every 64th position votes whether one of
 // its candidates is longer than `longLen`.  Factors that reach over many segments are what
-// keeps the segmented passes from settling.  counters[10] += votes.
+// keeps the segmented passes from settling.  counters[10] += votes for `longLen`,
+// counters[11] += votes for `midLen` (factors longer than the warm-up pass sees).
 __global__ void __launch_bounds__(256) k_longcount(const int4 *__restrict__ cand, const uint32_t *__restrict__ blkN,
-                                                   int logS, uint32_t total, int longLen, uint32_t *__restrict__ counters)
+                                                   int logS, uint32_t total, int longLen, int midLen,
+                                                   uint32_t *__restrict__ counters)
 {
     const uint32_t i = blockIdx.x * 256 + threadIdx.x;
-    bool vote = false;
+    bool vote = false, vote2 = false;
     if (i < total) {
         const uint32_t g = i * 64 + 17;
         const uint32_t b = g >> logS, p = g & ((1u << logS) - 1);
         if (p >= 1 && p + 8 < blkN[b]) {
             const int4 c = cand[g];
             vote = c.y >= longLen || c.w >= longLen;
+            vote2 = c.y >= midLen || c.w >= midLen;
         }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, vote);
+    const unsigned m = __ballot_sync(0xffffffffu, vote), m2 = __ballot_sync(0xffffffffu, vote2);
     if (m && (threadIdx.x & 31) == 0) atomicAdd(&counters[10], __popc(m));
+    if (m2 && (threadIdx.x & 31) == 0) atomicAdd(&counters[11], __popc(m2));
 }
 
 // Before the first pass: every base = 9 n_b (the all-literal estimate in d-space,
@@ -445,22 +456,28 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     // positions); a cut only pays when it is at least 4-fold (two passes of the chains +
     // the parallel check against one pass).
     int segLog = bd.logS, K = 1;
+    uint32_t warm = 0;
     {
         const int slots = ws.numSMs * SALZ_PARSE_CTAS * NCH;
-        int want = ws.parseSegments ? ws.parseSegments : 8 * slots / std::max(1, bd.B);
-        if (!ws.parseSegments && want < 4) want = 1;
-        const uint32_t minSeg = ws.parseSegments ? 16u * PC : 64u * PC;
-        if (!ws.parseSegments && want >= 4) {
+        const int userK = abs(ws.parseSegments);  // < 0: that many segments and the warm-up pass (tests)
+        int want = userK ? userK : 8 * slots / std::max(1, bd.B);
+        if (!userK && want < 4) want = 1;
+        const uint32_t minSeg = userK ? 16u * PC : 64u * PC;
+        if (!userK && want >= 4) {
             // inputs with long factors (deep repeats, runs) settle one segment per pass: keep them whole
             const uint32_t samples = (uint32_t)(((size_t)bd.B << bd.logS) / 64);
-            if (cudaMemsetAsync(ws.counters + 10, 0, 4, st) != cudaSuccess) return -1;
-            k_longcount<<<(samples + 255) / 256, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, samples, 4096, ws.counters);
+            if (cudaMemsetAsync(ws.counters + 10, 0, 8, st) != cudaSuccess) return -1;
+            k_longcount<<<(samples + 255) / 256, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, samples, 4096,
+                                                               WARM_CHUNKS * PC / 4, ws.counters);
             lc.launches += 1;
-            if (cudaMemcpyAsync(ws.h_counters + 10, ws.counters + 10, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+            if (cudaMemcpyAsync(ws.h_counters + 10, ws.counters + 10, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
             if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
             if ((uint64_t)ws.h_counters[10] * 2000 > bd.M / 64) want = 1;
+            if ((uint64_t)ws.h_counters[11] * 2000 <= bd.M / 64) warm = WARM_CHUNKS;
         }
         while (2 * K <= want && K < KMAX && (bd.S >> 1) >> (bd.logS - segLog) >= minSeg) { K *= 2; segLog--; }
+        if ((1u << segLog) < 4u * WARM_CHUNKS * PC) warm = 0;  // short segments: the full pass costs little more
+        if (ws.parseSegments < 0) warm = std::max(1u, std::min(WARM_CHUNKS, (1u << segLog) / PC / 2));
     }
     // The d values stay relative to the segment bases: cost[p] = dr[p] + segBase[p >> segLog] - 9p
     // (salz_cuda_debug_stages converts; nothing downstream needs the absolute costs).
@@ -476,12 +493,18 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
         while ((1 << kLog) < K) kLog++;
         const uint32_t chains = (uint32_t)bd.B << kLog;
         if (cudaMemsetAsync(old, 0, arrBytes, st) != cudaSuccess) return -1;  // all-literal estimate: d = base everywhere
-        // Text settles in two passes.  An input that has not after MAX_PASSES (factors reaching over
-        // many segments: one exact segment more per pass) gets the plain one-chain-per-block pass.
-        constexpr int MAX_PASSES = 3;
+        if (warm && cudaMemsetAsync(cur, 0, arrBytes, st) != cudaSuccess) return -1;  // the warm-up pass writes its windows only
+        // Text settles in two passes, and what the second pass reads of the first is the left
+        // end of every segment: the first pass walks only the leftmost WARM_CHUNKS chunks of a
+        // segment (its values are relative to the end of that window; the bases k_seg_scan
+        // derives from them are consistent with that).  An input that has not settled after
+        // MAX_PASSES (factors reaching over many segments: one exact segment more per pass) gets
+        // the plain one-chain-per-block pass.
+        const int MAX_PASSES = warm ? 4 : 3;
         for (int pass = 1; pass <= MAX_PASSES && !done; pass++) {
             k_parse<<<(chains + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, kLog, chains,
-                                                                                 ws.numSMs, cur, old, ws.segBase);
+                                                                                 pass == 1 ? warm : 0u, ws.numSMs, cur, old,
+                                                                                 ws.segBase);
             k_seg_scan<<<(bd.B + 63) / 64, 64, 0, st>>>(ws.blkN, bd.B, bd.logS, segLog, cur, ws.segBase);
             lc.launches += 2;
             if (pass >= 2) {
@@ -504,7 +527,7 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     }
     if (!done) {
         k_parse<<<(bd.B + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, 0, (uint32_t)bd.B,
-                                                                           ws.numSMs, cur, old, ws.segBase);
+                                                                           0u, ws.numSMs, cur, old, ws.segBase);
         k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.counters);
         lc.launches += 2;
     }

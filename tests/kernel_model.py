@@ -222,12 +222,14 @@ def post_bits(l):
     return ((l - 3) >> 3) + 4
 
 
-def parse_model(cand, N, seg_len=256, max_passes=3):
+def parse_model(cand, N, seg_len=256, max_passes=3, warm=0):
     """Model of parse.cu: the chain in the shifted space d[p] = cost[p] + 9p (one min per
     position), the block cut into segments of `seg_len` positions that keep d relative to
     their right end and read everything to their right from the PREVIOUS pass's array
     (k_parse + k_seg_scan), the parallel check that the recurrence holds everywhere
     (k_choose) from the second pass on, and after `max_passes` the plain single chain.
+    warm > 0: the first pass walks only the leftmost `warm` positions of every segment
+    (values relative to the end of that window, the rest of the array stays 0).
     Returns cost[n+1], choice[N,2], jump[N], passes (0 = fell back to one chain)."""
     n = N - 8
     w = {}
@@ -241,11 +243,13 @@ def parse_model(cand, N, seg_len=256, max_passes=3):
         c = cand[p]
         return [(o, l) for (o, l) in ((int(c[0]), int(c[1])), (int(c[2]), int(c[3]))) if l >= 3]
 
-    def run_pass(seg, old, base):
+    def run_pass(seg, old, base, window=0):
         K = (N + seg - 1) // seg
         new = np.zeros(N + 1, np.int64)
         for j in range(K):                       # independent CTAs
             L, R = j * seg, min(N, (j + 1) * seg)
+            if window:
+                R = min(R, L + window)
             d = INF if R == N else 0
             for p in range(R - 1, L - 1, -1):
                 if p > n:
@@ -290,8 +294,8 @@ def parse_model(cand, N, seg_len=256, max_passes=3):
     if K > 1:
         old = np.zeros(N + 1, np.int64)          # all-literal estimate: d = base everywhere
         base = np.full(K, 9 * n, np.int64)
-        for passes in range(1, max_passes + 1):
-            dr, base = run_pass(seg, old, base)
+        for passes in range(1, max_passes + (2 if warm else 1)):
+            dr, base = run_pass(seg, old, base, warm if passes == 1 else 0)
             if passes >= 2:
                 choice, bad = choose(seg, dr, base)
                 if bad == 0:

@@ -109,11 +109,12 @@ def test_medium_cases_all_stages(enc, orc):
         _check_stages(enc, orc, name, data)
 
 
-@pytest.mark.parametrize("k", [1, 2, 8, 64])
+@pytest.mark.parametrize("k", [1, 2, 8, 64, -4, -64])
 def test_parse_segments_exact_for_every_cut(enc, orc, k):
     """The segmented parse (estimates to the right of a segment, passes until nothing
     changes) must give the reference's (offs, len, cost) and bytes for any number of
-    segments, on text, deep repeats, one long factor and incompressible data."""
+    segments, on text, deep repeats, one long factor and incompressible data.  k < 0 forces
+    the shortened first pass (only the left end of every segment is walked)."""
     enc.set_parse_segments(k)
     try:
         cases = [("eng1M", synth.english_like(1 << 20, seed=11)),
