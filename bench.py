@@ -317,7 +317,7 @@ def main():
     # serial-chain parse took that place from the radix pass, the sort pass follows in "roofline_others".
     traffic = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_v6_traffic.json")))
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_v9_traffic.json")))
     except (OSError, ValueError):
         pass
 
@@ -330,12 +330,13 @@ def main():
     sort_launches = max(1, st["sort_launches"])
     parse_launches = max(1, args.steps * ((nblocks + batch - 1) // batch))
     cands = [
-        {"kernel": "k_parse", "bound": "hbm", "alg_bytes": 28.0 * positions, "ms": st["ms_parse"],
-         "launches": parse_launches, "traffic": (2 * tr("k_parse") + tr("k_choose") + tr("k_jump"))
-         if tr("k_parse") and tr("k_choose") and tr("k_jump") else None,
-         "note": "whole parse stage per batch (k_parse x2 passes + k_choose + k_jump; its CUDA-event time): serial "
-                 "(min,+) chains, 4 per consumer warp, issue/latency-bound by construction; 28 B/position = "
-                 "candidates 16 + cost 4 + choice 8; traffic = sum over the stage's launches"},
+        {"kernel": "k_parse", "bound": "hbm", "alg_bytes": 32.0 * positions, "ms": st["ms_parse"],
+         "launches": parse_launches, "traffic": (tr("k_parse_warm") + tr("k_parse") + tr("k_choose"))
+         if tr("k_parse_warm") and tr("k_parse") and tr("k_choose") else None,
+         "note": "whole parse stage per batch (k_parse: shortened first pass + full pass, k_choose incl. the jump "
+                 "pointers; its CUDA-event time): serial (min,+) chains, 4 per consumer warp, 16 per SM, "
+                 "latency-bound by construction; 32 B/position = candidates 16 + cost 4 + choice 8 + jump 4; "
+                 "traffic = sum over the stage's launches"},
         {"kernel": "k_scatter", "bound": "hbm", "alg_bytes": sort_bytes, "ms": st["ms_sort"],
          "launches": sort_launches, "traffic": tr("k_scatter<1, 0>"),
          "note": "one LSD radix pass: 16 B per list element (read + write of a packed element)"},

@@ -2,7 +2,7 @@
 //
 //   k_parse: right-to-left shortest-path DP with the reference's cost model and
 //            strict '<' tie-break order literal, PSV, NSV (ref lib/salz.c:562-662).
-//   k_jump : chunk-exit pointers of the chosen parse for the token walk in emit.cu.
+//   (k_choose also leaves the chunk-exit pointers of the chosen parse for the token walk in emit.cu.)
 #include "salz_dev.cuh"
 
 #include <algorithm>
@@ -362,51 +362,11 @@ __global__ void k_seg_scan(const uint32_t *__restrict__ blkN, int B, int logS, i
 __global__ void __launch_bounds__(256) k_choose(const int4 *__restrict__ cand, const uint32_t *__restrict__ blkN,
                                                 int logS, int segLog, const int32_t *__restrict__ dr,
                                                 const int32_t *__restrict__ segBase, int2 *__restrict__ choice,
-                                                uint32_t *__restrict__ counters)
+                                                uint32_t *__restrict__ jump, uint32_t *__restrict__ counters)
 {
-    const uint32_t g = blockIdx.x * 256 + threadIdx.x;
-    const uint32_t b = g >> logS, p = g & ((1u << logS) - 1);
-    const uint32_t N = blkN[b];
-    bool bad = false;
-    if (p < N) {
-        const uint32_t n = N - 8;
-        const size_t gb = (size_t)b << logS;
-        const int32_t *drb = dr + gb;
-        const int32_t *sb = segBase + b * KMAX;
-        uint32_t bo = 0, bl = 1;
-        if (p <= n) {
-            const int32_t mine = drb[p] + sb[p >> segLog];
-            int32_t best = 9 * (int32_t)n;  // d[n] = cost[n] + 9n = 9n (ref lib/salz.c:621)
-            if (p < n) {
-                best = drb[p + 1] + sb[(p + 1) >> segLog];
-                if (p >= 1) {  // position 0 is a forced literal
-                    const int4 c = cand[gb + p];
-                    if (c.y >= 3) {
-                        const uint32_t t = p + (uint32_t)c.y;
-                        const int32_t v = drb[t] + sb[t >> segLog] + factor_cost_bits((uint32_t)c.x, (uint32_t)c.y) - 9 * c.y;
-                        if (v < best) { best = v; bo = (uint32_t)c.x; bl = (uint32_t)c.y; }
-                    }
-                    if (c.w >= 3) {
-                        const uint32_t t = p + (uint32_t)c.w;
-                        const int32_t v = drb[t] + sb[t >> segLog] + factor_cost_bits((uint32_t)c.z, (uint32_t)c.w) - 9 * c.w;
-                        if (v < best) { best = v; bo = (uint32_t)c.z; bl = (uint32_t)c.w; }
-                    }
-                }
-            }
-            bad = mine != best;
-        }
-        choice[gb + p] = make_int2((int)bo, (int)bl);
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, bad);
-    if (m && (threadIdx.x & 31) == 0) atomicAdd(&counters[9], __popc(m));
-}
-
-// jump[p] = first position >= the end of p's PARSE_CHUNK that the chosen parse
-// reaches from p (pointer jumping inside the chunk; used by the token walk in
-// emit.cu).  One CTA per chunk.
-__global__ void __launch_bounds__(256) k_jump(const uint32_t *__restrict__ blkN, const int2 *__restrict__ choice,
-                                              int logS, uint32_t *__restrict__ jump)
-{
+    // One CTA per PARSE_CHUNK positions.  Second half: jump[p] = first position >= the end
+    // of p's chunk that the chosen parse reaches from p (pointer jumping inside the chunk;
+    // used by the token walk in emit.cu).
     __shared__ uint32_t nxt[PARSE_CHUNK];
     const uint32_t chunksPerBlock = 1u << (logS - PARSE_CHUNK_LOG);
     const uint32_t b = blockIdx.x / chunksPerBlock, c = blockIdx.x % chunksPerBlock;
@@ -414,15 +374,46 @@ __global__ void __launch_bounds__(256) k_jump(const uint32_t *__restrict__ blkN,
     const uint32_t base = c << PARSE_CHUNK_LOG;
     if (base >= N) return;
     const uint32_t end = min(N, base + PARSE_CHUNK);
+    const uint32_t n = N - 8;
     const size_t gb = (size_t)b << logS;
+    const int32_t *drb = dr + gb;
+    const int32_t *sb = segBase + b * KMAX;
     constexpr int PER = PARSE_CHUNK / 256;
     uint32_t v[PER];
+    int4 cd[PER];
+    int32_t mine[PER], lit[PER];
 #pragma unroll
     for (int i = 0; i < PER; i++) {
-        uint32_t p = base + threadIdx.x + i * 256;
-        v[i] = (p < end) ? p + (uint32_t)choice[gb + p].y : end;
+        const uint32_t p = base + threadIdx.x + i * 256;
+        cd[i] = (p >= 1 && p < n) ? cand[gb + p] : make_int4(0, 0, 0, 0);  // position 0 is a forced literal
+        mine[i] = (p <= n) ? drb[p] + sb[p >> segLog] : 0;
+        lit[i] = (p < n) ? drb[p + 1] + sb[(p + 1) >> segLog] : 9 * (int32_t)n;  // d[n] = cost[n] + 9n = 9n (ref lib/salz.c:621)
+    }
+    bool bad = false;
+#pragma unroll
+    for (int i = 0; i < PER; i++) {
+        const uint32_t p = base + threadIdx.x + i * 256;
+        uint32_t bo = 0, bl = 1;
+        if (p <= n) {
+            int32_t best = lit[i];
+            if (cd[i].y >= 3) {
+                const uint32_t t = p + (uint32_t)cd[i].y;
+                const int32_t w = drb[t] + sb[t >> segLog] + factor_cost_bits((uint32_t)cd[i].x, (uint32_t)cd[i].y) - 9 * cd[i].y;
+                if (w < best) { best = w; bo = (uint32_t)cd[i].x; bl = (uint32_t)cd[i].y; }
+            }
+            if (cd[i].w >= 3) {
+                const uint32_t t = p + (uint32_t)cd[i].w;
+                const int32_t w = drb[t] + sb[t >> segLog] + factor_cost_bits((uint32_t)cd[i].z, (uint32_t)cd[i].w) - 9 * cd[i].w;
+                if (w < best) { best = w; bo = (uint32_t)cd[i].z; bl = (uint32_t)cd[i].w; }
+            }
+            bad |= mine[i] != best;
+        }
+        if (p < end) choice[gb + p] = make_int2((int)bo, (int)bl);
+        v[i] = (p < end) ? p + bl : end;
         nxt[threadIdx.x + i * 256] = v[i];
     }
+    const unsigned m = __ballot_sync(0xffffffffu, bad);
+    if (m && (threadIdx.x & 31) == 0) atomicAdd(&counters[9], __popc(m));
     __syncthreads();
     for (int it = 0; it < PARSE_CHUNK_LOG; it++) {
         bool moved = false;
@@ -436,7 +427,7 @@ __global__ void __launch_bounds__(256) k_jump(const uint32_t *__restrict__ blkN,
     }
 #pragma unroll
     for (int i = 0; i < PER; i++) {
-        uint32_t p = base + threadIdx.x + i * 256;
+        const uint32_t p = base + threadIdx.x + i * 256;
         if (p < end) jump[gb + p] = v[i];
     }
 }
@@ -483,7 +474,7 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     // (salz_cuda_debug_stages converts; nothing downstream needs the absolute costs).
     // Two arrays: a pass reads what lies right of a segment from the previous pass's array.
     int32_t *cur = ws.cost, *old = ws.cost2;
-    const uint32_t chooseGrid = (uint32_t)(((size_t)bd.B << bd.logS) / 256);
+    const uint32_t chooseGrid = (uint32_t)bd.B << (bd.logS - PARSE_CHUNK_LOG);
     const size_t arrBytes = ((size_t)bd.B << bd.logS) * sizeof(int32_t);
     bool done = false;
     k_seg_init<<<(bd.B * KMAX + 255) / 256, 256, 0, st>>>(ws.blkN, bd.B, ws.segBase);
@@ -509,7 +500,7 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
             lc.launches += 2;
             if (pass >= 2) {
                 if (cudaMemsetAsync(ws.counters + 9, 0, 4, st) != cudaSuccess) return -1;
-                k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.counters);
+                k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.jump, ws.counters);
                 lc.launches += 1;
                 if (cudaMemcpyAsync(ws.h_counters + 9, ws.counters + 9, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
                 if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
@@ -528,13 +519,11 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
     if (!done) {
         k_parse<<<(bd.B + NCH - 1) / NCH, PARSE_THREADS, PARSE_SMEM, st>>>(ws.cand, ws.blkN, bd.logS, segLog, 0, (uint32_t)bd.B,
                                                                            0u, ws.numSMs, cur, old, ws.segBase);
-        k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.counters);
+        k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.jump, ws.counters);
         lc.launches += 2;
     }
     ws.parseSegLog = segLog;
     ws.parseDr = cur;
-    k_jump<<<bd.B << (bd.logS - PARSE_CHUNK_LOG), 256, 0, st>>>(ws.blkN, ws.choice, bd.logS, ws.jump);
-    lc.launches += 1;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "salz_cuda: parse_build: %s\n", cudaGetErrorString(e));
