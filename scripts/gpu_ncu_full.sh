@@ -7,7 +7,7 @@ CMD="python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu0.log 2>&1
 echo "ncu0 exit $?"
-ncu --set full --clock-control none -k regex:'k_scatter|k_local|k_parse|k_choose|k_rerank_apply|k_ansv_tile|k_plcp_irreducible|k_plcp_apply|k_init|k_emit_tokens|k_jump' -c 48 -f -o /tmp/prof_main $CMD > gpurun_out/ncu1.log 2>&1
+ncu --set full --clock-control none -k regex:'k_scatter|k_local|k_parse|k_choose|k_rerank_apply|k_ansv_tile|k_plcp_irreducible|k_plcp_apply|k_init|k_emit_tokens' -c 48 -f -o /tmp/prof_main $CMD > gpurun_out/ncu1.log 2>&1
 echo "ncu1 exit $?"
 ncu -i /tmp/prof_main.ncu-rep --page raw --csv > gpurun_out/main_raw.csv 2>/dev/null
 ncu --set full --clock-control none --import-source on -k regex:'k_parse|k_ansv_tile|k_plcp_irreducible' -c 3 -f -o /tmp/prof_src $CMD > gpurun_out/ncu2.log 2>&1
