@@ -33,20 +33,60 @@ __device__ __forceinline__ TokBits token_bits(int2 c)
     return tb;
 }
 
-// One thread per block: follow the chunk-exit pointers from position 0.
-__global__ void k_chunk_entries(const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ jump, int logS,
-                                int B, uint32_t *__restrict__ chunkEntry)
+// Chunk entries: the positions e_0 = 0, e_{i+1} = jump[e_i] and the chunks they fall in -
+// a chain of dependent loads per block (512 for a 1 MiB block), cut short by exact
+// speculation.  One warp per block; lane j walks the chunks of range j from the range's
+// first position (lane 0: position 0, the true chain).  The true chain then goes through
+// the ranges in order: where it steps on a position the range's lane has visited, the rest
+// of that lane's walk IS the true chain (the walk is a function of the position) and its
+// exit is taken over; until then it walks by itself and erases what the lane had left.
+// Paths merge within a chunk or two, so the chain is ~16 + 3 x 31 loads long.
+// chunkEntry is NONE everywhere before the launch.  grid = B, 32 threads.
+__global__ void __launch_bounds__(32) k_chunk_entries(const uint32_t *__restrict__ blkN,
+                                                      const uint32_t *__restrict__ jump, int logS,
+                                                      uint32_t *chunkEntry)
 {
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
+    __shared__ uint32_t ex[32];
+    const uint32_t b = blockIdx.x, lane = threadIdx.x;
     const uint32_t N = blkN[b];
     const size_t gb = (size_t)b << logS;
     uint32_t *ce = chunkEntry + (gb >> PARSE_CHUNK_LOG);
-    uint32_t e = 0;
-    while (e < N) {
-        ce[e >> PARSE_CHUNK_LOG] = e;
-        e = jump[gb + e];
+    const uint32_t chunks = (N + PARSE_CHUNK - 1) >> PARSE_CHUNK_LOG;
+    const uint32_t perRange = (chunks + 31) / 32;
+    {
+        uint32_t e = (lane * perRange) << PARSE_CHUNK_LOG;
+        const uint32_t lim = min(N, ((lane + 1) * perRange) << PARSE_CHUNK_LOG);
+        while (e < lim) {
+            ce[e >> PARSE_CHUNK_LOG] = e;
+            e = jump[gb + e];
+        }
+        ex[lane] = e;
     }
+    __threadfence_block();
+    __syncwarp();
+    if (lane != 0) return;
+    uint32_t x = ex[0];
+    uint32_t clean = min(chunks, perRange);  // chunks below this hold their final value
+    while (x < N) {
+        uint32_t c = x >> PARSE_CHUNK_LOG;
+        const uint32_t j = c / perRange, rEnd = min(chunks, (j + 1) * perRange);
+        for (uint32_t k = clean; k < c; k++) ce[k] = NONE;  // chunks the chain has jumped over
+        for (;;) {
+            if (__ldcg(&ce[c]) == x) {  // on the lane's path: the rest of range j is final
+                x = ex[j];
+                break;
+            }
+            const uint32_t nx = jump[gb + x];
+            const uint32_t c2 = (nx < N) ? nx >> PARSE_CHUNK_LOG : chunks;  // N itself may lie inside the last chunk
+            ce[c] = x;
+            for (uint32_t k = c + 1; k < min(c2, rEnd); k++) ce[k] = NONE;
+            x = nx;
+            c = c2;
+            if (c >= rEnd) break;
+        }
+        clean = rEnd;
+    }
+    for (uint32_t k = clean; k < chunks; k++) ce[k] = NONE;
 }
 
 // One thread per chunk: count the tokens that start in the chunk and their bits.
@@ -278,7 +318,7 @@ int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,
     const uint32_t totalChunks = (uint32_t)(total >> PARSE_CHUNK_LOG);
     const uint32_t chunksPerBlock = bd.S >> PARSE_CHUNK_LOG;
     cudaMemsetAsync(ws.chunkEntry, 0xff, (size_t)totalChunks * 4, st);
-    k_chunk_entries<<<(bd.B + 31) / 32, 32, 0, st>>>(ws.blkN, ws.jump, bd.logS, bd.B, ws.chunkEntry);
+    k_chunk_entries<<<bd.B, 32, 0, st>>>(ws.blkN, ws.jump, bd.logS, ws.chunkEntry);
     k_walk_count<<<(totalChunks + 127) / 128, 128, 0, st>>>(ws.blkN, ws.choice, ws.chunkEntry, bd.logS,
                                                             totalChunks, ws.chunkTok, ws.chunkBits);
     k_block_scan<<<bd.B, 256, 0, st>>>(ws.blkN, chunksPerBlock, ws.chunkTok, ws.chunkBits, ws.blkTokens,

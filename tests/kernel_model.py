@@ -317,6 +317,47 @@ def parse_model(cand, N, seg_len=256, max_passes=3, warm=0):
 
 
 # -------------------------------------------------------------- emit.cu ----
+def chunk_entries_model(jump, N, chunk=CHUNK, lanes=32):
+    """k_chunk_entries: the chain e_0 = 0, e_{i+1} = jump[e_i] by exact speculation.  Lane j
+    walks range j of the chunks from the range's first position; the true chain takes a
+    lane's walk over where it steps on a position that lane has visited and walks (and
+    erases) by itself until then.  Returns entry[chunk] (-1 = no token starts there)."""
+    NONE = -1
+    nch = (N + chunk - 1) // chunk
+    per = (nch + lanes - 1) // lanes
+    ce = [NONE] * nch
+    ex = [0] * lanes
+    for j in range(lanes):                      # phase 1, all lanes at once
+        e, lim = j * per * chunk, min(N, (j + 1) * per * chunk)
+        while e < lim:
+            ce[e // chunk] = e
+            e = int(jump[e])
+        ex[j] = e
+    x, clean = ex[0], min(nch, per)             # phase 2, lane 0
+    while x < N:
+        c = x // chunk
+        j = c // per
+        rend = min(nch, (j + 1) * per)
+        for k in range(clean, c):
+            ce[k] = NONE
+        while True:
+            if ce[c] == x:
+                x = ex[j]
+                break
+            nx = int(jump[x])
+            c2 = nx // chunk if nx < N else nch
+            ce[c] = x
+            for k in range(c + 1, min(c2, rend)):
+                ce[k] = NONE
+            x, c = nx, c2
+            if c >= rend:
+                break
+        clean = rend
+    for k in range(clean, nch):
+        ce[k] = NONE
+    return ce
+
+
 def emit_model(T, N, choice, jump):
     """Chunk walk + closed-form layout.  Returns the encoded block (bytes)."""
     NONE = -1
@@ -326,6 +367,7 @@ def emit_model(T, N, choice, jump):
     while e < N:
         entry[e >> 11] = e
         e = int(jump[e])
+    assert entry == chunk_entries_model(jump, N)
 
     def tok_bits(o, l):
         return (1, 0) if l == 1 else (pre_bits(o), post_bits(l))

@@ -105,6 +105,11 @@ def test_medium_cases_all_stages(enc, orc):
              ("dna1M", synth.dna_like(1 << 20, seed=7)),
              ("a1M", np.full(1 << 20, 0x61, np.uint8)),
              ("rand1M", synth.uniform_random(1 << 20, seed=4))]
+    # factors that jump over many parse chunks between stretches of ordinary text (the chunk-entry
+    # chain of emit.cu is walked speculatively per range of chunks and must survive being skipped)
+    eng = synth.english_like(400000, seed=17)
+    cases.append(("eng_longcopies", np.concatenate([eng[:200000], eng[:150000], eng[200000:260000],
+                                                    eng[100000:190000], eng[260000:], eng[:70000]])))
     for name, data in cases:
         _check_stages(enc, orc, name, data)
 

@@ -102,3 +102,28 @@ def test_kernel_model_matches_oracle(port):
         # the shortened first pass (left end of every segment only) changes nothing in the result
         cost2, choice2, _, _ = km.parse_model(st["cand"], len(a), seg_len=128, warm=32)
         assert np.array_equal(choice2[1:n], choice[1:n]) and np.array_equal(cost2[1:n], cost[1:n]), name
+
+
+def test_chunk_entry_speculation_is_exact():
+    """The speculative chunk-entry chain (emit.cu k_chunk_entries) against the plain chain on
+    random step functions: short steps (paths merge), long jumps over ranges, both mixed."""
+    rng = np.random.default_rng(5)
+    for trial in range(60):
+        chunk = int(rng.choice([4, 8, 16]))
+        lanes = int(rng.choice([2, 4, 8]))
+        N = int(rng.integers(1, 600))
+        kind = trial % 3
+        step = rng.integers(1, 4, N) if kind == 0 else rng.integers(1, 3 * chunk * lanes, N) if kind == 1 else \
+            np.where(rng.random(N) < 0.05, rng.integers(1, 200, N), rng.integers(1, 3, N))
+        # jump[p] = first position >= the end of p's chunk on the path p, p + step[p], ...
+        jump = np.zeros(N, np.int64)
+        for p in range(N - 1, -1, -1):
+            t = min(N, p + int(step[p]))
+            end = min(N, (p // chunk + 1) * chunk)
+            jump[p] = t if t >= end else jump[t]
+        want = [-1] * ((N + chunk - 1) // chunk)
+        e = 0
+        while e < N:
+            want[e // chunk] = e
+            e = int(jump[e])
+        assert km.chunk_entries_model(jump, N, chunk, lanes) == want, (trial, chunk, lanes, N)
