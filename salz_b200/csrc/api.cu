@@ -340,6 +340,8 @@ static int stream_common(salz_cuda_ctx *c, const uint8_t *src, bool srcOnDevice,
 // buffers, so that the upload of batch i+1 and the download of batch i-1 run under the
 // kernels of batch i.  A stream that would fit one batch is cut in two for the same reason.
 // (Pageable host memory makes the copies synchronous; the result is the same.)
+constexpr int SPLIT_PCT = 25;  // share of a one-batch stream that goes into its first piece
+
 static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, size_t block_len, uint8_t *dst,
                        size_t dst_cap, size_t *dst_len, uint32_t *block_sizes, size_t *nblocks_out)
 {
@@ -351,13 +353,19 @@ static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, siz
     const size_t tail = src_len - (nblocks - 1) * block_len;
     if (tail <= 8) { set_err(c, "last block has %zu bytes (<= 8): not encodable", tail); return -1; }
     cudaStream_t st = c->stream, cs = c->copyStream;
-    size_t per = ws.Bmax;
-    if (nblocks <= ws.Bmax && nblocks >= 32) per = (nblocks + 1) / 2;
-    const size_t nbatch = (nblocks + per - 1) / per;
-    auto batch_bytes = [&](size_t i) {
-        const size_t off = i * per * block_len;
-        return std::min(src_len - off, per * block_len);
-    };
+    // Batches of Bmax blocks; a stream that fits one batch is cut in two so that most of its
+    // upload and download run under kernels.  The first piece is the smaller one: its upload is
+    // the copy nothing can hide.
+    std::vector<size_t> cut;  // cut[i] = first block of batch i, cut[nbatch] = nblocks
+    for (size_t b = 0; b < nblocks; b += ws.Bmax) cut.push_back(b);
+    cut.push_back(nblocks);
+    if (cut.size() == 2 && nblocks >= 32) {
+        static const int pct = [] { const char *e = getenv("SALZ_SPLIT_PCT"); int v = e ? atoi(e) : 0; return (v > 0 && v < 100) ? v : SPLIT_PCT; }();
+        cut.insert(cut.begin() + 1, std::max<size_t>(16, nblocks * pct / 100));
+    }
+    const size_t nbatch = cut.size() - 1;
+    auto batch_off = [&](size_t i) { return cut[i] * block_len; };
+    auto batch_bytes = [&](size_t i) { return std::min(src_len, cut[i + 1] * block_len) - cut[i] * block_len; };
     struct Restore {
         salz_cuda_ctx *c;
         ~Restore() { c->ws.T = c->Tbuf[0]; c->ws.out = c->outbuf[0]; }
@@ -371,10 +379,10 @@ static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, siz
     bool outBusy[2] = {false, false};
     for (size_t i = 0; i < nbatch; i++) {
         const int k = (int)(i & 1);
-        const size_t b0 = i * per;
-        const int B = (int)std::min(per, nblocks - b0);
+        const size_t b0 = cut[i];
+        const int B = (int)(cut[i + 1] - b0);
         if (i + 1 < nbatch) {  // Tbuf[k^1] was batch i-1's text: its kernels are complete (run_batch synchronises)
-            CKC(c, cudaMemcpyAsync(c->Tbuf[k ^ 1], src + (i + 1) * per * block_len, batch_bytes(i + 1),
+            CKC(c, cudaMemcpyAsync(c->Tbuf[k ^ 1], src + batch_off(i + 1), batch_bytes(i + 1),
                                    cudaMemcpyHostToDevice, cs));
             CKC(c, cudaEventRecord(c->tReady[k ^ 1], cs));
         }

@@ -188,7 +188,7 @@ def test_batched_stream_matches_per_block_oracle(enc, orc):
 
 def test_pipelined_host_stream_paths(orc):
     """salz_cuda_encode_stream with host buffers overlaps copies and kernels (two text and
-    two output buffers): a stream that fits one batch is cut in two, a longer one runs
+    two output buffers): a stream that fits one batch is cut in two (1:3), a longer one runs
     batch after batch; pinned and pageable memory; the device-resident entry on the same
     context afterwards.  All must give the per-block reference records."""
     import torch
@@ -203,7 +203,7 @@ def test_pipelined_host_stream_paths(orc):
             want += len(blk).to_bytes(4, "little") + blk
         stream, sizes = e.encode_stream(data, bl)
         assert stream == want
-        short = data[: 40 * bl + 999]                                            # 41 blocks: one batch, cut in two
+        short = data[: 40 * bl + 999]                                            # 41 blocks: one batch, cut in two (16 + 25)
         nrec = 0
         pos = 0
         for _ in range(41):
@@ -225,7 +225,7 @@ def test_pipelined_host_stream_paths(orc):
         assert e.encode(data[:bl]) == orc.encode(data[:bl])
     finally:
         e.close()
-    # other batch capacities: one batch cut in two (68 + 68) / two full batches (ragged last block)
+    # other batch capacities: one batch cut in two (34 + 102) / two full batches (ragged last block)
     for bmax in (160, 68):
         e = salz_b200.SalzCuda(0, bl, bmax)
         try:
