@@ -562,6 +562,9 @@ k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ vals
 // changes); the SA slot of element k is  group(k) + (k - index of its pst),
 // and the new group id is the slot of the element's head.
 
+#ifndef SALZ_RERANK_FUSED
+#define SALZ_RERANK_FUSED 1
+#endif
 struct HK { uint32_t head, pst, keep; };  // head/pst: list index + 1 of the last flagged element (0 none)
 
 __device__ __forceinline__ HK hk_combine(HK a, HK b)
@@ -720,6 +723,68 @@ __global__ void __launch_bounds__(1024) k_rerank_scan(uint32_t *__restrict__ agg
     }
 }
 
+// Tile state of the single-pass re-rank (decoupled look-back inside a block's tiles): one
+// 16-byte word per tile, written and read whole (x = head | pst << 32, y = keep | status << 32).
+constexpr uint32_t RR_AGG = 1, RR_PREFIX = 2;
+__device__ __forceinline__ void rr_publish(ulonglong2 *st, HK v, uint32_t status)
+{
+    const unsigned long long x = (unsigned long long)v.head | ((unsigned long long)v.pst << 32);
+    const unsigned long long y = (unsigned long long)v.keep | ((unsigned long long)status << 32);
+    asm volatile("st.global.cg.v2.u64 [%0], {%1, %2};" ::"l"(st), "l"(x), "l"(y) : "memory");
+}
+__device__ __forceinline__ uint32_t rr_peek(const ulonglong2 *st, HK &v)
+{
+    unsigned long long x, y;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(st) : "memory");
+    v.head = (uint32_t)x;
+    v.pst = (uint32_t)(x >> 32);
+    v.keep = (uint32_t)y;
+    return (uint32_t)(y >> 32);
+}
+
+// Exclusive prefix of tile `tile` over the tiles of its block before it (lt of them); warp 0
+// of the CTA calls it with the tile's own aggregate.  Lane l looks at tile - 1 - l.
+__device__ __forceinline__ HK rr_lookback(ulonglong2 *state, uint32_t tile, uint32_t lt, HK agg, int lane)
+{
+    if (lt == 0) {
+        if (lane == 0) rr_publish(state + tile, agg, RR_PREFIX);
+        return HK{0, 0, 0};
+    }
+    if (lane == 0) rr_publish(state + tile, agg, RR_AGG);
+    HK acc = {0, 0, 0};
+    uint32_t done = 0;  // predecessors already folded into acc
+    for (;;) {
+        const uint32_t back = done + (uint32_t)lane + 1;  // distance of my tile
+        const bool valid = back <= lt;
+        HK v = {0, 0, 0};
+        uint32_t status = RR_PREFIX;
+        if (valid) {
+            do { status = rr_peek(state + (tile - back), v); } while (status == 0);
+        }
+        const unsigned pm = __ballot_sync(0xffffffffu, valid && status == RR_PREFIX);
+        const unsigned vm = __ballot_sync(0xffffffffu, valid);
+        const int stop = pm ? __ffs(pm) - 1 : 31;  // nearest tile that holds a prefix
+        if (!valid || lane > stop) v = HK{0, 0, 0};
+        // ordered fold: farther tiles first
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            HK t;
+            t.head = __shfl_down_sync(0xffffffffu, v.head, o);
+            t.pst = __shfl_down_sync(0xffffffffu, v.pst, o);
+            t.keep = __shfl_down_sync(0xffffffffu, v.keep, o);
+            if (lane + o < 32) v = hk_combine(t, v);
+        }
+        v.head = __shfl_sync(0xffffffffu, v.head, 0);
+        v.pst = __shfl_sync(0xffffffffu, v.pst, 0);
+        v.keep = __shfl_sync(0xffffffffu, v.keep, 0);
+        acc = hk_combine(v, acc);
+        if (pm || vm != 0xffffffffu) break;  // reached a prefix or the block's first tile
+        done += 32;
+    }
+    if (lane == 0) rr_publish(state + tile, hk_combine(acc, agg), RR_PREFIX);
+    return acc;
+}
+
 template <bool PACKED, bool ROUND0>
 __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
                                                      ListView lv, int logS, const uint32_t *__restrict__ aggHead,
@@ -728,9 +793,10 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
                                                      uint64_t *__restrict__ rank, uint32_t *__restrict__ SA,
                                                      uint64_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut,
                                                      const uint32_t *__restrict__ cntBefore,
-                                                     uint32_t *__restrict__ cntNext)
+                                                     uint32_t *__restrict__ cntNext, ulonglong2 *lookState)
 {
     __shared__ HK scratch[WARPS + 1];
+    __shared__ HK tilePrefix;
     const TileLoc tl = locate(lv, blockIdx.x);
     const uint32_t segRemain = lv.cnt[tl.b] - tl.lt * TILE;
     const uint32_t i0 = threadIdx.x * ITEMS;
@@ -750,13 +816,25 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
     }
     HK agg;
     HK ex = hk_block_excl(v, &agg, scratch);
-    ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, ex);
+    uint32_t keepBase;  // survivors of the block's earlier tiles
+    if (lookState) {    // single pass: the prefix over the block's earlier tiles by look-back
+        if (threadIdx.x < 32) {
+            const HK pre = rr_lookback(lookState, blockIdx.x, tl.lt, agg, (int)threadIdx.x);
+            if (threadIdx.x == 0) tilePrefix = pre;
+        }
+        __syncthreads();
+        ex = hk_combine(tilePrefix, ex);
+        keepBase = 0;
+    } else {
+        ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, ex);
+        keepBase = aggKeep[lv.tileBase[tl.b]];
+    }
     if (threadIdx.x == 0 && agg.keep) atomicAdd(&cntNext[tl.b], agg.keep);
     // survivors are appended, in list order, behind what the block's next list already
     // holds (cntBefore: a snapshot taken before this launch; null = nothing)
     const size_t gb = (size_t)tl.b << logS;
     uint32_t curHead = ex.head, curPst = ex.pst;
-    uint32_t outPos = (uint32_t)gb + (cntBefore ? cntBefore[tl.b] : 0u) + (ex.keep - aggKeep[lv.tileBase[tl.b]]);
+    uint32_t outPos = (uint32_t)gb + (cntBefore ? cntBefore[tl.b] : 0u) + (ex.keep - keepBase);
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         if (i0 + i < tl.valid) {
@@ -1189,13 +1267,24 @@ int rerank(SortCtx &s, int v, uint32_t count, uint32_t tiles, int src, int dst, 
     Workspace &ws = s.ws;
     const int logS = s.bd.logS;
     const ListView lv = view(ws, v);
+#if SALZ_RERANK_FUSED
+    // single pass: tile prefixes by look-back (the scatter passes' tile state is free by now)
+    ulonglong2 *look = (ulonglong2 *)ws.tileState;
+    CK(cudaMemsetAsync(look, 0, (size_t)tiles * sizeof(ulonglong2), s.st));
+    k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, ws.aggHead, ws.aggPst,
+                                                           ws.aggKeep, round, ws.rank, ws.SA, ws.keys[dst],
+                                                           ws.vals[dst & 1], cntBefore, ws.listCnt[vNext], look);
+    s.lc.launches += 1;
+    s.algBytes += (uint64_t)count * (PACKED ? 20 : 28);
+#else
     k_rerank_reduce<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], lv, logS, ws.aggHead, ws.aggPst, ws.aggKeep);
     k_rerank_scan<<<1, 1024, 0, s.st>>>(ws.aggHead, ws.aggPst, ws.aggKeep, tiles);
     k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, ws.aggHead, ws.aggPst,
                                                            ws.aggKeep, round, ws.rank, ws.SA, ws.keys[dst],
-                                                           ws.vals[dst & 1], cntBefore, ws.listCnt[vNext]);
+                                                           ws.vals[dst & 1], cntBefore, ws.listCnt[vNext], nullptr);
     s.lc.launches += 3;
     s.algBytes += (uint64_t)count * (PACKED ? 28 : 36);
+#endif
     CK(cudaGetLastError());
     if (dbg(s, "rerank")) return -1;
     return 0;

@@ -1,7 +1,7 @@
 #!/bin/bash
-for pct in 50 35 25 15; do echo "=== split $pct"; SALZ_SPLIT_PCT=$pct timeout 600 python bench.py --steps 4 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
-import sys, json
-for l in sys.stdin:
-    if l.startswith('{'):
-        d = json.loads(l); print('value %.1f MB/s e2e %.1f ms %.2f' % (d['value'], d['e2e']['value'], d['e2e']['ms_per_step']))
-"; done
+mkdir -p gpurun_out
+cp variants/b_fused.so salz_b200/libsalz_cuda.so
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+bash scripts/gpu_variants.sh
+cp variants/b_fused.so salz_b200/libsalz_cuda.so
+timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --workload english256 --level 9 | grep -o "stage_ms_per_step[^}]*}"
