@@ -49,7 +49,8 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
                                                   const uint32_t *__restrict__ blkN, int logS,
                                                   int2 *__restrict__ cand2, uint64_t *__restrict__ farItems,
                                                   uint32_t *__restrict__ farCount, int32_t *__restrict__ tileMinV,
-                                                  int32_t *__restrict__ tileMinL)
+                                                  int32_t *__restrict__ tileMinL, int32_t *__restrict__ pyrSA1,
+                                                  int32_t *__restrict__ pyrLCP1)
 {
     __shared__ uint32_t sv[AT * APAD];   // (value << 8) | link
     __shared__ int32_t sm[AT * APAD];    // LCP, then the element's running minimum
@@ -62,11 +63,14 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     const uint32_t b = blockIdx.x / tilesPerBlock, tb = blockIdx.x % tilesPerBlock;
     const uint32_t n = blkN[b] - 8;
     const uint32_t t0 = tb * ATS;  // first slot of the tile (local)
+    const size_t gb = (size_t)b << logS;
+    const size_t pyr1 = ((gb + t0) >> 5) + tid;  // my segment is one group of the level-1 pyramid
     if (t0 >= n) {
         if (tid == 0) { tileMinV[blockIdx.x] = AINF; tileMinL[blockIdx.x] = AINF; }
+        pyrSA1[pyr1] = AINF;
+        pyrLCP1[pyr1] = AINF;
         return;
     }
-    const size_t gb = (size_t)b << logS;
     int2 *cd = cand2 + 2 * gb;
     int4 *cd4 = (int4 *)cd;
 
@@ -118,6 +122,8 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         segLen[tid] = (uint8_t)len;
         segMin[tid] = (lastPM >= 0) ? (int32_t)(sv[sb + lastPM] >> 8) : AINF;
         segLcp[tid] = lmin;
+        pyrSA1[pyr1] = segMin[tid];  // minima over 32 consecutive SA slots (AINF past n): level 1 of the
+        pyrLCP1[pyr1] = lmin;        // pyramids k_ansv_far walks
     }
     __syncthreads();
     // exclusive prefix / suffix minima over the tile's segments: an element smaller
@@ -360,7 +366,8 @@ int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounte
     uint64_t *farItems = ws.keys[0];  // the sort buffers are free once the suffix array is complete
     cudaMemsetAsync(farCount, 0, 4, st);
     k_ansv_tile<<<(uint32_t)(total / ATS), AT, 0, st>>>(ws.SA, ws.lcp, ws.blkN, bd.logS, (int2 *)ws.cand, farItems,
-                                                        farCount, ws.tileMinV, ws.tileMinL);
+                                                        farCount, ws.tileMinV, ws.tileMinL, ws.pyrSA[1], ws.pyrLCP[1]);
+    if (pyramid_upper_build(ws, bd, st, lc)) return -1;
     k_ansv_tilescan<<<bd.B, 32, 0, st>>>(ws.tileMinV, bd.S / ATS, ws.tilePreV, ws.tileSufV);
     k_ansv_far<<<148 * 8, 256, 0, st>>>(py, ws.blkN, farItems, farCount, (int2 *)ws.cand, ws.tilePreV, ws.tileSufV);
     k_cand0<<<(bd.B + 127) / 128, 128, 0, st>>>(ws.cand, bd.logS, bd.B);

@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) k_plcp_scan_tiles(int32_t *__restrict__ t
 }
 
 // PLCP[g] = inclusive-max(V)[g] - p, also scattered to LCP[ISA[g]] (gathering
-// LCP[i] = PLCP[SA[i]] in k_pyramid_l1 instead measured the same).
+// LCP[i] = PLCP[SA[i]] in SA order instead measured the same).
 __global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ blkN,
                                                    const uint64_t *__restrict__ rank, int logS,
                                                    const int32_t *__restrict__ tileMax, int32_t *__restrict__ V,
@@ -202,29 +202,6 @@ __global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ 
     }
 }
 
-// level-1 pyramid: minima over groups of 32 consecutive SA slots.
-__global__ void __launch_bounds__(256) k_pyramid_l1(const uint32_t *__restrict__ blkN,
-                                                    const uint32_t *__restrict__ SA,
-                                                    const int32_t *__restrict__ lcp, int logS,
-                                                    int32_t *__restrict__ outSA, int32_t *__restrict__ outLCP)
-{
-    const uint32_t Smask = (1u << logS) - 1;
-    const uint32_t s = blockIdx.x * 256 + threadIdx.x;
-    const uint32_t b = s >> logS, r = s & Smask;
-    const uint32_t n = blkN[b] - 8;
-    int32_t a = (r < n) ? (int32_t)SA[s] : 0x7fffffff;
-    int32_t l = (r < n) ? lcp[s] : 0x7fffffff;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        a = min(a, __shfl_xor_sync(0xffffffffu, a, o));
-        l = min(l, __shfl_xor_sync(0xffffffffu, l, o));
-    }
-    if ((threadIdx.x & 31) == 0) {
-        outSA[s >> 5] = a;
-        outLCP[s >> 5] = l;
-    }
-}
-
 // level l+1 from level l (count = entries of the coarser level, all blocks).
 __global__ void __launch_bounds__(256) k_pyramid_up(const int32_t *__restrict__ inSA,
                                                     const int32_t *__restrict__ inLCP, uint32_t outCount,
@@ -257,10 +234,19 @@ int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter
                                              ws.tileMax);
     k_plcp_scan_tiles<<<bd.B, 256, 0, st>>>(ws.tileMax, tilesPerBlock);
     k_plcp_apply<<<tiles, LT, 0, st>>>(ws.blkN, ws.rank, bd.logS, ws.tileMax, ws.plcp, ws.lcp);
-    k_pyramid_l1<<<(uint32_t)(total / 256), 256, 0, st>>>(ws.blkN, ws.SA, ws.lcp, bd.logS, ws.pyrSA[1],
-                                                          ws.pyrLCP[1]);
-    lc.launches += 4;
-    // coarser levels: level l has (S >> 5l) entries per block; stop once <= 32
+    lc.launches += 3;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        fprintf(stderr, "salz_cuda: lcp_build: %s\n", cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}
+
+// Pyramid levels 2.. from level 1 (which k_ansv_tile writes: its per-thread segments are
+// the groups of 32 slots): level l has (S >> 5l) entries per block; stop once <= 32.
+int pyramid_upper_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
+{
     int l = 1;
     while ((bd.S >> (5 * l)) > 32) {
         size_t fine = (size_t)bd.B * (bd.S >> (5 * l));
@@ -270,10 +256,5 @@ int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter
         lc.launches += 1;
         l++;
     }
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) {
-        fprintf(stderr, "salz_cuda: lcp_build: %s\n", cudaGetErrorString(e));
-        return -1;
-    }
-    return 0;
+    return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }

@@ -646,6 +646,7 @@ __device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, co
     }
 }
 
+#if !SALZ_RERANK_FUSED
 template <bool PACKED, bool ROUND0>
 __global__ void __launch_bounds__(TT) k_rerank_reduce(const uint64_t *__restrict__ keys, ListView lv, int logS,
                                                       uint32_t *__restrict__ aggHead, uint32_t *__restrict__ aggPst,
@@ -722,6 +723,7 @@ __global__ void __launch_bounds__(1024) k_rerank_scan(uint32_t *__restrict__ agg
         s = hk_combine(s, c);
     }
 }
+#endif
 
 // Tile state of the single-pass re-rank (decoupled look-back inside a block's tiles): one
 // 16-byte word per tile, written and read whole (x = head | pst << 32, y = keep | status << 32).

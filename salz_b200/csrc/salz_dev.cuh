@@ -152,6 +152,7 @@ int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st,
              LaunchCounter &lc, uint64_t &algBytes, int &rounds, float *msSort);
 // lcp.cu
 int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
+int pyramid_upper_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
 // ansv.cu
 int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
 // parse.cu
