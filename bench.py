@@ -141,6 +141,37 @@ def run_cpu_reference(data, block_len, nblocks_sample, threads):
     return time.perf_counter() - t0, nbytes, kind
 
 
+def run_cpu_libsais(data, block_len, nblocks_sample, threads):
+    """SA only, beside the device SA stage (CPU baseline iii): upstream
+    `libsais()` from oracle/_ref on the same blocks -- one thread, one block per thread
+    on all host cores, and `libsais_omp(threads)` block after block.  GB/s of text, or
+    None without the compiled reference."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle.binding import Ref
+    if not Ref.available():
+        return None
+    ref = Ref()
+    nblocks = (len(data) + block_len - 1) // block_len
+    blocks = [data[b * block_len: (b + 1) * block_len] for b in range(min(nblocks, nblocks_sample))]
+    blocks = [b[: len(b) - 8] for b in blocks if len(b) > 8]   # the reference sorts T[0..N-8)
+    out = {"blocks": len(blocks), "threads": threads}
+    one = blocks[: max(1, min(4, len(blocks)))]
+    t0 = time.perf_counter()
+    for b in one:
+        ref.suffix_array(b)
+    out["libsais_1thread_GBps"] = sum(len(b) for b in one) / (time.perf_counter() - t0) / 1e9
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(ref.suffix_array, blocks))
+    out["libsais_block_per_thread_GBps"] = sum(len(b) for b in blocks) / (time.perf_counter() - t0) / 1e9
+    omp = blocks[: max(1, min(16, len(blocks)))]
+    t0 = time.perf_counter()
+    for b in omp:
+        ref.suffix_array(b, threads=threads)
+    out["libsais_omp_GBps"] = sum(len(b) for b in omp) / (time.perf_counter() - t0) / 1e9
+    return out
+
+
 def reference_arm(args, kind, mib, block_len, desc):
     """bench.py --impl reference: the reference CPU implementation on the host cores."""
     rank = int(os.environ.get("RANK", "0"))
@@ -366,6 +397,7 @@ def main():
         nb1 = min(nblocks, 4)
         s1, b1, _ = run_cpu_reference(data, block_len, nb1, 1)
         cpu["single_thread_value"] = b1 / s1 / 1e6
+        cpu["sa"] = run_cpu_libsais(data, block_len, nb, cores)
 
     n_in = st["input_bytes"]
     value = world * size * args.steps / (ms_dev * 1e-3) / 1e6
