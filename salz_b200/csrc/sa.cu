@@ -788,7 +788,7 @@ __device__ __forceinline__ HK rr_lookback(ulonglong2 *state, uint32_t tile, uint
 }
 
 template <bool PACKED, bool ROUND0>
-__global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+__global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
                                                      ListView lv, int logS, const uint32_t *__restrict__ aggHead,
                                                      const uint32_t *__restrict__ aggPst,
                                                      const uint32_t *__restrict__ aggKeep, uint32_t round,
@@ -799,6 +799,7 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
 {
     __shared__ HK scratch[WARPS + 1];
     __shared__ HK tilePrefix;
+    __shared__ uint64_t stage[PACKED ? TILE : 1];   // survivors of the tile, compacted
     const TileLoc tl = locate(lv, blockIdx.x);
     const uint32_t segRemain = lv.cnt[tl.b] - tl.lt * TILE;
     const uint32_t i0 = threadIdx.x * ITEMS;
@@ -817,49 +818,84 @@ __global__ void __launch_bounds__(TT) k_rerank_apply(const uint64_t *__restrict_
         }
     }
     HK agg;
-    HK ex = hk_block_excl(v, &agg, scratch);
+    const HK exLoc = hk_block_excl(v, &agg, scratch);   // exclusive inside the tile
+    const size_t gb = (size_t)tl.b << logS;
+    // Round 0: the one pst of a segment is its first element, whatever the tile.
+    const uint32_t pst0 = tl.first - tl.lt * TILE + 1;
+    // Elements whose head (and pst) lie inside the tile do not need the prefix over the
+    // earlier tiles: their rank (and SA slot, for singletons) leaves before the look-back
+    // barrier, so the scatter overlaps the wait for the predecessors.
+    auto early = [&]() {
+        uint32_t curHead = exLoc.head, curPst = ROUND0 ? pst0 : exLoc.pst;
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            if (i0 + i < tl.valid) {
+                const uint32_t k = tl.first + i0 + i;
+                if (head[i]) curHead = k + 1;
+                if (!ROUND0 && pst[i]) curPst = k + 1;
+                if (curHead && curPst) {
+                    uint32_t p, prim;
+                    if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
+                    else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
+                    const uint32_t r = prim + (curHead - curPst);
+                    rank[gb + p] = rk_make(round, prim, r);
+                    if (head[i] && head[i + 1]) SA[gb + r] = p;
+                }
+            }
+        }
+    };
+    HK ex;
     uint32_t keepBase;  // survivors of the block's earlier tiles
     if (lookState) {    // single pass: the prefix over the block's earlier tiles by look-back
         if (threadIdx.x < 32) {
             const HK pre = rr_lookback(lookState, blockIdx.x, tl.lt, agg, (int)threadIdx.x);
             if (threadIdx.x == 0) tilePrefix = pre;
         }
+        early();   // warp 0 after its look-back, the other warps while it waits
         __syncthreads();
-        ex = hk_combine(tilePrefix, ex);
+        ex = hk_combine(tilePrefix, exLoc);
         keepBase = 0;
     } else {
-        ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, ex);
+        early();
+        ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, exLoc);
         keepBase = aggKeep[lv.tileBase[tl.b]];
     }
     if (threadIdx.x == 0 && agg.keep) atomicAdd(&cntNext[tl.b], agg.keep);
     // survivors are appended, in list order, behind what the block's next list already
-    // holds (cntBefore: a snapshot taken before this launch; null = nothing)
-    const size_t gb = (size_t)tl.b << logS;
+    // holds (cntBefore: a snapshot taken before this launch; null = nothing); packed
+    // elements are compacted in shared memory first and leave as coalesced runs
     uint32_t curHead = ex.head, curPst = ex.pst;
-    uint32_t outPos = (uint32_t)gb + (cntBefore ? cntBefore[tl.b] : 0u) + (ex.keep - keepBase);
+    uint32_t locHead = exLoc.head, locPst = ROUND0 ? pst0 : exLoc.pst;   // what early() saw
+    const uint32_t outBase = (uint32_t)gb + (cntBefore ? cntBefore[tl.b] : 0u) + (ex.keep - exLoc.keep - keepBase);
+    uint32_t outLoc = exLoc.keep;
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         if (i0 + i < tl.valid) {
             const uint32_t k = tl.first + i0 + i;
-            if (head[i]) curHead = k + 1;
-            if (pst[i]) curPst = k + 1;
+            if (head[i]) { curHead = k + 1; locHead = k + 1; }
+            if (pst[i]) { curPst = k + 1; if (!ROUND0) locPst = k + 1; }
+            const bool done = locHead && locPst;
             uint32_t p, prim;
             if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
             else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
             const uint32_t r = prim + (curHead - curPst);  // SA slot of the group head
-            rank[gb + p] = rk_make(round, prim, r);
+            if (!done) rank[gb + p] = rk_make(round, prim, r);
             if (head[i] && head[i + 1]) {
-                SA[gb + r] = p;
+                if (!done) SA[gb + r] = p;
             } else {
                 if (PACKED) {
-                    keysOut[outPos] = ((uint64_t)r << (2 * logS)) | p;
+                    stage[outLoc] = ((uint64_t)r << (2 * logS)) | p;
                 } else {
-                    keysOut[outPos] = (uint64_t)r << logS;
-                    valsOut[outPos] = p;
+                    keysOut[outBase + outLoc] = (uint64_t)r << logS;
+                    valsOut[outBase + outLoc] = p;
                 }
-                outPos++;
+                outLoc++;
             }
         }
+    }
+    if (PACKED) {
+        __syncthreads();
+        for (uint32_t j = threadIdx.x; j < agg.keep; j += TT) keysOut[outBase + j] = stage[j];
     }
 }
 
