@@ -612,23 +612,24 @@ __device__ __forceinline__ HK hk_block_excl(HK v, HK *agg, HK *scratch /*[WARPS+
 }
 
 // Flags of the ITEMS elements a thread owns (consecutive), plus head of the next one.
-template <bool PACKED, bool ROUND0>
-__device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, const TileLoc &tl, uint32_t segRemain,
-                                           uint32_t i0, int logS, uint64_t e[ITEMS], bool head[ITEMS + 1],
-                                           bool pst[ITEMS])
+// fetch(idx) returns the element at tile-relative index idx (-1 .. TILE).
+template <bool PACKED, bool ROUND0, typename Fetch>
+__device__ __forceinline__ void load_flags_from(Fetch fetch, const TileLoc &tl, uint32_t segRemain,
+                                                uint32_t i0, int logS, uint64_t e[ITEMS], bool head[ITEMS + 1],
+                                                bool pst[ITEMS])
 {
     // key field and group of an element
     const uint64_t secMask = ((uint64_t)1 << logS) - 1;
     auto kf = [&](uint64_t x) -> uint64_t { return PACKED ? (x >> logS) : x; };
     const bool havePrev = (tl.lt > 0 || i0 > 0) && i0 < tl.valid;
-    uint64_t prev = havePrev ? kf(keys[tl.first + i0 - 1]) : 0;
+    uint64_t prev = havePrev ? kf(fetch((int)i0 - 1)) : 0;
 #pragma unroll
     for (int i = 0; i <= ITEMS; i++) {
         const uint32_t idx = i0 + i;
         // idx may be one past the tile: still inside the segment when segRemain allows
         const bool exists = (i < ITEMS) ? (idx < tl.valid) : (idx < tl.valid || (idx == TILE && segRemain > TILE));
         if (exists) {
-            const uint64_t raw = keys[tl.first + idx];
+            const uint64_t raw = fetch((int)idx);
             const uint64_t cur = kf(raw);
             const bool first = (tl.lt == 0 && idx == 0);
             bool p = first, hd = first || prev != cur;
@@ -645,6 +646,19 @@ __device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, co
         }
     }
 }
+
+template <bool PACKED, bool ROUND0>
+__device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, const TileLoc &tl, uint32_t segRemain,
+                                           uint32_t i0, int logS, uint64_t e[ITEMS], bool head[ITEMS + 1],
+                                           bool pst[ITEMS])
+{
+    load_flags_from<PACKED, ROUND0>([&](int idx) { return keys[tl.first + idx]; }, tl, segRemain, i0, logS, e, head, pst);
+}
+
+// Tile staged in shared memory: element idx (-1 .. TILE) lives at rr_phys(idx + 1); the
+// padding makes a thread's ITEMS consecutive elements conflict-free across the warp.
+__device__ __forceinline__ int rr_phys(int x) { return x + x / ITEMS; }
+constexpr int RR_STAGE = TILE + 2 + (TILE + 2) / ITEMS + 1;
 
 #if !SALZ_RERANK_FUSED
 template <bool PACKED, bool ROUND0>
@@ -799,14 +813,22 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
 {
     __shared__ HK scratch[WARPS + 1];
     __shared__ HK tilePrefix;
-    __shared__ uint64_t stage[PACKED ? TILE : 1];   // survivors of the tile, compacted
+    __shared__ uint64_t stage[RR_STAGE];   // the tile's elements (coalesced load), later its survivors, compacted
     const TileLoc tl = locate(lv, blockIdx.x);
     const uint32_t segRemain = lv.cnt[tl.b] - tl.lt * TILE;
     const uint32_t i0 = threadIdx.x * ITEMS;
     const uint32_t Smask = (1u << logS) - 1;
     uint64_t e[ITEMS];
     bool head[ITEMS + 1], pst[ITEMS];
-    load_flags<PACKED, ROUND0>(keys, tl, segRemain, i0, logS, e, head, pst);
+    {
+        // elements -1 (last of the previous tile) .. valid (first of the next tile), where they exist
+        const int lo = (tl.lt > 0) ? -1 : 0;
+        const int hi = (int)tl.valid + ((tl.valid == TILE && segRemain > TILE) ? 1 : 0);
+        for (int idx = lo + (int)threadIdx.x; idx < hi; idx += TT) stage[rr_phys(idx + 1)] = keys[(int64_t)tl.first + idx];
+        __syncthreads();
+        load_flags_from<PACKED, ROUND0>([&](int idx) { return stage[rr_phys(idx + 1)]; }, tl, segRemain, i0, logS, e,
+                                        head, pst);
+    }
     HK v = {0, 0, 0};
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
