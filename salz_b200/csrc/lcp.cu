@@ -43,6 +43,14 @@ constexpr int IT = 256;
 #ifndef SALZ_PLCP_CTAS
 #define SALZ_PLCP_CTAS 6
 #endif
+// PI positions per thread (IT apart), their three dependent gathers (rank -> SA -> text)
+// issued stage by stage so that PI chains are in flight per thread: the kernel is bound by
+// the latency of those gathers, not by any throughput.
+#ifndef SALZ_PLCP_ITEMS
+#define SALZ_PLCP_ITEMS 2
+#endif
+constexpr int PI = SALZ_PLCP_ITEMS;
+static_assert(LT % (IT * PI) == 0, "a CTA's positions must lie in one tile");
 __global__ void __launch_bounds__(IT, SALZ_PLCP_CTAS) k_plcp_irreducible(const uint8_t *__restrict__ T, size_t Tstride,
                                                          const uint32_t *__restrict__ blkN,
                                                          const uint64_t *__restrict__ rank,
@@ -50,87 +58,115 @@ __global__ void __launch_bounds__(IT, SALZ_PLCP_CTAS) k_plcp_irreducible(const u
                                                          int32_t *__restrict__ V, int32_t *__restrict__ tileMax)
 {
     const uint32_t Smask = (1u << logS) - 1;
-    const uint32_t g = blockIdx.x * IT + threadIdx.x;
-    const uint32_t b = g >> logS, p = g & Smask;
+    const uint32_t g0 = blockIdx.x * (IT * PI) + threadIdx.x;
+    const uint32_t b = g0 >> logS;   // S is a multiple of IT * PI: one block per CTA
     const uint32_t n = blkN[b] - 8;  // blkN >= 9 for every block of a batch
     const uint8_t *Tb = T + (size_t)b * Tstride;
     const int lane = threadIdx.x & 31;
 
-    int32_t v = 0;
-    uint32_t q = 0, cap = 0, l = 0;
-    bool pending = false;
-    if (p < n) {
-        uint32_t r = (g & ~Smask) | ((uint32_t)rank[g] & 0xffffffu);  // padded global slot
-        if ((r & Smask) == 0) {
-            v = (int32_t)p;  // smallest suffix of the block: PLCP = 0
-        } else {
-            q = SA[r - 1];
-            cap = n - max(p, q);
-            if (p == 0 || q == 0) {
-                l = lcp_private(Tb + p, Tb + q, cap, 32);
-                pending = (l == 32 && cap > 32);
-                v = (int32_t)(l + p);
+    uint32_t p[PI], q[PI], cap[PI], l[PI], r[PI];
+    int32_t v[PI];
+    bool pending[PI], live[PI], cmp[PI];
+    uint64_t rk[PI], xa[PI], xb[PI];
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        p[k] = (g0 + k * IT) & Smask;
+        live[k] = p[k] < n;
+        rk[k] = live[k] ? rank[g0 + k * IT] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        r[k] = (uint32_t)rk[k] & 0xffffffu;   // block-local slot
+        live[k] = live[k] && r[k] != 0;       // slot 0 = smallest suffix of the block: PLCP = 0
+        q[k] = live[k] ? SA[(g0 & ~Smask) + r[k] - 1] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        // one load per side: the preceding byte (irreducible if it differs) and the first
+        // 7 bytes of the comparison
+        cmp[k] = live[k] && p[k] != 0 && q[k] != 0;
+        xa[k] = cmp[k] ? load_u64_unaligned(Tb + p[k] - 1) : 0;
+        xb[k] = cmp[k] ? load_u64_unaligned(Tb + q[k] - 1) : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        v[k] = 0;
+        l[k] = 0;
+        cap[k] = 0;
+        pending[k] = false;
+        if (p[k] < n && r[k] == 0) v[k] = (int32_t)p[k];
+        if (live[k]) {
+            cap[k] = n - max(p[k], q[k]);
+            if (!cmp[k]) {
+                l[k] = lcp_private(Tb + p[k], Tb + q[k], cap[k], 32);
+                pending[k] = (l[k] == 32 && cap[k] > 32);
+                v[k] = (int32_t)(l[k] + p[k]);
             } else {
-                // one load per side: the preceding byte (irreducible if it differs) and
-                // the first 7 bytes of the comparison
-                const uint64_t x = load_u64_unaligned(Tb + p - 1) ^ load_u64_unaligned(Tb + q - 1);
+                const uint64_t x = xa[k] ^ xb[k];
                 if (x & 0xffu) {
                     const uint64_t y = x >> 8;
                     if (y) {
-                        l = min((uint32_t)(__ffsll((long long)y) - 1) >> 3, cap);
+                        l[k] = min((uint32_t)(__ffsll((long long)y) - 1) >> 3, cap[k]);
                     } else {
-                        l = 7;
-                        if (cap > 7) l += lcp_private(Tb + p + 7, Tb + q + 7, cap - 7, 32);
-                        else l = cap;
-                        pending = (l == 39 && cap > 39);
+                        l[k] = 7;
+                        if (cap[k] > 7) l[k] += lcp_private(Tb + p[k] + 7, Tb + q[k] + 7, cap[k] - 7, 32);
+                        else l[k] = cap[k];
+                        pending[k] = (l[k] == 39 && cap[k] > 39);
                     }
-                    v = (int32_t)(l + p);
+                    v[k] = (int32_t)(l[k] + p[k]);
                 }
             }
         }
     }
     // Long matches: the whole warp compares 32 x 16 bytes per step.
-    unsigned todo = __ballot_sync(0xffffffffu, pending);
-    while (todo) {
-        int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        uint32_t p0 = __shfl_sync(0xffffffffu, p, src);
-        uint32_t q0 = __shfl_sync(0xffffffffu, q, src);
-        uint32_t cap0 = __shfl_sync(0xffffffffu, cap, src);
-        uint32_t l0 = __shfl_sync(0xffffffffu, l, src);
-        for (;;) {
-            uint32_t off = l0 + lane * 16;
-            uint32_t mine = 16;  // matching bytes in my 16-byte window
-            if (off < cap0) {
-                uint64_t x = load_u64_unaligned(Tb + p0 + off) ^ load_u64_unaligned(Tb + q0 + off);
-                if (x) {
-                    mine = (uint32_t)(__ffsll((long long)x) - 1) >> 3;
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        unsigned todo = __ballot_sync(0xffffffffu, pending[k]);
+        while (todo) {
+            int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            uint32_t p0 = __shfl_sync(0xffffffffu, p[k], src);
+            uint32_t q0 = __shfl_sync(0xffffffffu, q[k], src);
+            uint32_t cap0 = __shfl_sync(0xffffffffu, cap[k], src);
+            uint32_t l0 = __shfl_sync(0xffffffffu, l[k], src);
+            for (;;) {
+                uint32_t off = l0 + lane * 16;
+                uint32_t mine = 16;  // matching bytes in my 16-byte window
+                if (off < cap0) {
+                    uint64_t x = load_u64_unaligned(Tb + p0 + off) ^ load_u64_unaligned(Tb + q0 + off);
+                    if (x) {
+                        mine = (uint32_t)(__ffsll((long long)x) - 1) >> 3;
+                    } else {
+                        uint64_t y = load_u64_unaligned(Tb + p0 + off + 8) ^ load_u64_unaligned(Tb + q0 + off + 8);
+                        if (y) mine = 8 + ((uint32_t)(__ffsll((long long)y) - 1) >> 3);
+                    }
+                    mine = min(mine, cap0 - off);
                 } else {
-                    uint64_t y = load_u64_unaligned(Tb + p0 + off + 8) ^ load_u64_unaligned(Tb + q0 + off + 8);
-                    if (y) mine = 8 + ((uint32_t)(__ffsll((long long)y) - 1) >> 3);
+                    mine = 0;
                 }
-                mine = min(mine, cap0 - off);
-            } else {
-                mine = 0;
+                unsigned stop = __ballot_sync(0xffffffffu, mine < 16);
+                if (stop) {
+                    int first = __ffs(stop) - 1;
+                    uint32_t m = __shfl_sync(0xffffffffu, mine, first);
+                    l0 = l0 + first * 16 + m;
+                    break;
+                }
+                l0 += 512;
             }
-            unsigned stop = __ballot_sync(0xffffffffu, mine < 16);
-            if (stop) {
-                int first = __ffs(stop) - 1;
-                uint32_t m = __shfl_sync(0xffffffffu, mine, first);
-                l0 = l0 + first * 16 + m;
-                break;
-            }
-            l0 += 512;
+            l0 = min(l0, cap0);
+            if (lane == src) v[k] = (int32_t)(l0 + p[k]);
         }
-        l0 = min(l0, cap0);
-        if (lane == src) v = (int32_t)(l0 + p);
     }
-    V[g] = v;
+    int32_t mx = 0;
+#pragma unroll
+    for (int k = 0; k < PI; k++) {
+        V[g0 + k * IT] = v[k];
+        mx = max(mx, v[k]);
+    }
     // tile maximum
-    int32_t mx = v;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0 && mx > 0) atomicMax(&tileMax[g / LT], mx);
+    if (lane == 0 && mx > 0) atomicMax(&tileMax[g0 / LT], mx);
 }
 
 // One CTA per block: exclusive max-scan of the tile maxima, in place.
@@ -230,7 +266,7 @@ int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter
     const uint32_t tiles = (uint32_t)(total / LT);
     const uint32_t tilesPerBlock = bd.S / LT;
     if (cudaMemsetAsync(ws.tileMax, 0, (size_t)tiles * sizeof(int32_t), st) != cudaSuccess) return -1;
-    k_plcp_irreducible<<<tiles * (LT / IT), IT, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.rank, ws.SA, bd.logS, ws.plcp,
+    k_plcp_irreducible<<<tiles * (LT / (IT * PI)), IT, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.rank, ws.SA, bd.logS, ws.plcp,
                                              ws.tileMax);
     k_plcp_scan_tiles<<<bd.B, 256, 0, st>>>(ws.tileMax, tilesPerBlock);
     k_plcp_apply<<<tiles, LT, 0, st>>>(ws.blkN, ws.rank, bd.logS, ws.tileMax, ws.plcp, ws.lcp);
