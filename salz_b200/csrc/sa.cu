@@ -381,7 +381,10 @@ __global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ 
 // start at tileState + 256.
 constexpr size_t SCATTER_SMEM_PACKED = (size_t)TILE * 8 + 2 * (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 64;
 constexpr size_t SCATTER_SMEM_PAIRS = SCATTER_SMEM_PACKED + (size_t)TILE * 4;
-constexpr int SCATTER_MIN_CTAS = (TT * ITEMS <= 2048) ? 4 : 2;
+#ifndef SALZ_SCTAS
+#define SALZ_SCTAS ((SALZ_TT * SALZ_ITEMS <= 2048) ? 4 : 2)
+#endif
+constexpr int SCATTER_MIN_CTAS = SALZ_SCTAS;   // resident k_scatter CTAs per SM (register cap and grid size)
 
 template <bool PACKED, bool MATCH_ANY>
 __global__ void __launch_bounds__(TT, SCATTER_MIN_CTAS)
