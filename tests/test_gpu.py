@@ -293,30 +293,55 @@ def test_host_library_encode_roundtrip(orc):
     assert lib.salz_encode_safe(b"12345678", 8, C.create_string_buffer(100), C.byref(n)) == -1
 
 
-def test_full_size_roundtrip_properties(orc):
-    """Size-independent checks at a large size (64 MiB + 4096 English-like, level 5):
-    every block decodes back to its input, sizes sum up, sampled blocks equal the oracle."""
+def _stream_properties(orc, data, bl, sample):
+    """Size-independent checks of a whole stream: every record decodes back to its block
+    (host decoder), the sizes add up to the stream, sampled blocks equal the oracle's bytes."""
     lib = _host_lib()
-    bl = 1 << 20
-    data = synth.english_like((64 << 20) + 4096, seed=1)
-    e = salz_b200.SalzCuda(0, bl, 65)
+    nblocks = (len(data) + bl - 1) // bl
+    e = salz_b200.SalzCuda(0, bl, min(nblocks, max(1, (64 << 20) // bl + 1)))
     try:
         stream, sizes = e.encode_stream(data, bl)
     finally:
         e.close()
+    assert len(sizes) == nblocks
     assert len(stream) == int(sizes.astype(np.int64).sum()) + 4 * len(sizes)
     pos = 0
     back = C.create_string_buffer(bl + 8)
+    picks = {0, len(sizes) - 1} | {int(x) for x in sample if x < len(sizes)}
     for b, sz in enumerate(sizes.tolist()):
         assert int.from_bytes(stream[pos: pos + 4], "little") == sz
         rec = stream[pos + 4: pos + 4 + sz]
         blk = data[b * bl: (b + 1) * bl].tobytes()
         m = C.c_size_t(len(blk))
         assert lib.salz_decode_safe(rec, sz, back, C.byref(m)) == 0 and back.raw[: m.value] == blk, b
-        if b in (0, 17, 40, len(sizes) - 1):
+        if b in picks:
             assert rec == orc.encode(blk), b
         pos += 4 + sz
     assert pos == len(stream)
+
+
+def test_full_size_roundtrip_properties(orc):
+    """64 MiB + 4096 English-like, level 5 (the bench shape, BASELINE configs[1])."""
+    _stream_properties(orc, synth.english_like((64 << 20) + 4096, seed=1), 1 << 20, (17, 40))
+
+
+@pytest.mark.parametrize("kind,mib,level,sample", [
+    ("dna", 1024, 5, (3, 31, 700)),  # configs[2] at full size: planted repeats up to 2^19, ~20 doubling rounds
+    ("mixed", 256, 5, (7, 9, 20, 150)),  # configs[3] (one GPU's share): english / dna / random sections in one stream
+    ("single", 512, 5, (5, 300)),    # configs[4]a at full size: every round on the global path, one parse chain per block
+    ("random", 512, 5, (11, 400)),   # configs[4]b at full size: every block PLAIN
+    ("mixed", 48, 9, (1,)),           # 16 MiB blocks: pairs format
+    ("english", 32, 1, (100, 301)),   # 64 KiB blocks: hundreds of blocks per batch
+])
+def test_full_size_properties_other_shapes(orc, kind, mib, level, sample):
+    bl = 1 << (15 + level)
+    size = (mib << 20) + 4096
+    data = {"dna": lambda: synth.dna_like(size, seed=2, block=bl),
+            "mixed": lambda: synth.mixed_stream(size, seed=3),
+            "single": lambda: synth.single_byte(size),
+            "random": lambda: synth.uniform_random(size, seed=4),
+            "english": lambda: synth.english_like(size, seed=1)}[kind]()
+    _stream_properties(orc, data, bl, sample)
 
 
 def test_cli_compress_matches_reference_cli(tmp_path):
