@@ -213,6 +213,90 @@ __global__ void __launch_bounds__(128) k_emit_tokens(
     }
 }
 
+// One WARP per chunk (default; SALZ_EMIT_WARP=0 launches the one-thread-per-chunk form
+// above).  The thread-per-chunk walk is a chain of ~400 dependent 8-byte loads per thread,
+// 131 K chains each pulling single sectors out of a 2 GB array (1.6 TB/s of DRAM traffic at
+// 5 % issue utilisation), and its per-token stores are scattered across the threads.  Here
+// the warp loads the chunk's chosen lengths coalesced into shared memory (clamped to 16
+// bits: anything longer leaves the chunk anyway), lane 0 walks them there and leaves the
+// list of token positions, and then all lanes handle 32 tokens at a time: bit offsets by a
+// warp scan, tokPos / tokBit written as coalesced runs.  Same stores, same values.
+#ifndef SALZ_EMIT_WARP
+#define SALZ_EMIT_WARP 1
+#endif
+constexpr int EW = 4;   // warps (chunks) per CTA
+__global__ void __launch_bounds__(EW * 32) k_emit_tokens_warp(
+    const uint8_t *__restrict__ T, size_t Tstride, const uint32_t *__restrict__ blkN,
+    const int2 *__restrict__ choice, const uint32_t *__restrict__ chunkEntry, const uint32_t *__restrict__ chunkTok,
+    const uint32_t *__restrict__ chunkBits, const uint32_t *__restrict__ blkSalzLen,
+    const uint64_t *__restrict__ blkOutOff, int framing, int logS, uint32_t totalChunks,
+    uint32_t *__restrict__ tokPos, uint32_t *__restrict__ tokBit, uint32_t *__restrict__ firstTok,
+    uint8_t *__restrict__ out)
+{
+    __shared__ uint16_t slen[EW][PARSE_CHUNK];
+    __shared__ uint16_t stok[EW][PARSE_CHUNK];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t c = blockIdx.x * EW + w;
+    if (c >= totalChunks) return;
+    const uint32_t e = chunkEntry[c];
+    if (e == NONE) return;
+    const uint32_t b = c >> (logS - PARSE_CHUNK_LOG);
+    const uint32_t N = blkN[b];
+    if (blkSalzLen[b] > N + 4) return;  // PLAIN block
+    const size_t gb = (size_t)b << logS;
+    const uint8_t *Tb = T + (size_t)b * Tstride;
+    uint8_t *ob = out + blkOutOff[b] + (framing ? 4 : 0);
+    uint32_t *tp = tokPos + gb, *tbit = tokBit + gb;
+    uint32_t *ft = firstTok + (gb >> 2);
+    const uint32_t cs = (e >> PARSE_CHUNK_LOG) << PARSE_CHUNK_LOG;   // first position of the chunk
+    const uint32_t cnt = min(N, cs + PARSE_CHUNK) - cs;              // positions of the chunk inside the block
+    const int2 *chb = choice + gb + cs;
+    for (uint32_t j = lane; j < cnt; j += 32) slen[w][j] = (uint16_t)min((uint32_t)chb[j].y, 0xffffu);
+    __syncwarp();
+    uint32_t nt = 0;
+    if (lane == 0) {
+        uint32_t q = e - cs;
+        while (q < cnt) {
+            stok[w][nt++] = (uint16_t)q;
+            q += slen[w][q];
+        }
+    }
+    nt = __shfl_sync(0xffffffffu, nt, 0);
+    __syncwarp();
+    const uint32_t t0 = chunkTok[c];
+    uint32_t Bbase = chunkBits[c];
+    for (uint32_t i0 = 0; i0 < nt; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool live = i < nt;
+        uint32_t p = 0, bits = 0;
+        int2 ch = make_int2(0, 1);
+        TokBits tb = {0, 0};
+        if (live) {
+            p = cs + stok[w][i];
+            ch = choice[gb + p];
+            tb = token_bits(ch);
+            bits = (uint32_t)(tb.pre + tb.post);
+        }
+        uint32_t inc = bits;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        const uint32_t Bt = Bbase + inc - bits;
+        if (live) {
+            const uint32_t t = t0 + i;
+            tp[t] = p;
+            tbit[t] = Bt;
+            const uint32_t bytePos = 4 + t + 8 * ((Bt + tb.pre + 63) >> 6);
+            ob[bytePos] = (ch.y == 1) ? Tb[p] : (uint8_t)(((uint32_t)ch.x - 1u) & 0xffu);
+            const uint32_t Bn = Bt + bits;
+            for (uint32_t k = (Bt + 63) >> 6; k < ((Bn + 63) >> 6); k++) ft[k] = t;
+        }
+        Bbase += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
 // ORs the bits of a field into word `w`.  The field covers global bits
 // [s, s+nb) with its least significant bit last; the word covers [w0, w0+64).
 __device__ __forceinline__ void place_field(uint64_t &w, int64_t w0, int64_t s, int nb, uint64_t val)
@@ -324,9 +408,15 @@ int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,
     k_block_scan<<<bd.B, 256, 0, st>>>(ws.blkN, chunksPerBlock, ws.chunkTok, ws.chunkBits, ws.blkTokens,
                                        ws.blkBits, ws.blkSalzLen, ws.blkOutLen);
     k_out_offsets<<<1, 32, 0, st>>>(ws.blkOutLen, bd.B, framing, ws.blkOutOff);
+#if SALZ_EMIT_WARP
+    k_emit_tokens_warp<<<(totalChunks + EW - 1) / EW, EW * 32, 0, st>>>(
+        ws.T, bd.Tstride, ws.blkN, ws.choice, ws.chunkEntry, ws.chunkTok, ws.chunkBits, ws.blkSalzLen,
+        ws.blkOutOff, framing, bd.logS, totalChunks, ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
+#else
     k_emit_tokens<<<(totalChunks + 127) / 128, 128, 0, st>>>(
         ws.T, bd.Tstride, ws.blkN, ws.choice, ws.chunkEntry, ws.chunkTok, ws.chunkBits, ws.blkSalzLen,
         ws.blkOutOff, framing, bd.logS, totalChunks, ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
+#endif
     k_emit_words<<<(uint32_t)((total >> 2) / 256), 256, 0, st>>>(ws.blkN, ws.choice, ws.blkTokens, ws.blkBits,
                                                                  ws.blkSalzLen, ws.blkOutOff, framing, bd.logS,
                                                                  ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
