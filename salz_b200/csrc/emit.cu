@@ -173,6 +173,10 @@ __global__ void k_out_offsets(const uint32_t *__restrict__ blkOutLen, int B, int
     }
 }
 
+#ifndef SALZ_EMIT_WARP
+#define SALZ_EMIT_WARP 1
+#endif
+#if !SALZ_EMIT_WARP
 // One thread per chunk: assign token indices and bit offsets, write the
 // direct bytes, record which token owns the first bit of every word.
 __global__ void __launch_bounds__(128) k_emit_tokens(
@@ -212,6 +216,7 @@ __global__ void __launch_bounds__(128) k_emit_tokens(
         p += (uint32_t)ch.y;
     }
 }
+#endif
 
 // One WARP per chunk (default; SALZ_EMIT_WARP=0 launches the one-thread-per-chunk form
 // above).  The thread-per-chunk walk is a chain of ~400 dependent 8-byte loads per thread,
@@ -221,9 +226,7 @@ __global__ void __launch_bounds__(128) k_emit_tokens(
 // bits: anything longer leaves the chunk anyway), lane 0 walks them there and leaves the
 // list of token positions, and then all lanes handle 32 tokens at a time: bit offsets by a
 // warp scan, tokPos / tokBit written as coalesced runs.  Same stores, same values.
-#ifndef SALZ_EMIT_WARP
-#define SALZ_EMIT_WARP 1
-#endif
+#if SALZ_EMIT_WARP
 constexpr int EW = 4;   // warps (chunks) per CTA
 __global__ void __launch_bounds__(EW * 32) k_emit_tokens_warp(
     const uint8_t *__restrict__ T, size_t Tstride, const uint32_t *__restrict__ blkN,
@@ -296,6 +299,8 @@ __global__ void __launch_bounds__(EW * 32) k_emit_tokens_warp(
         Bbase += __shfl_sync(0xffffffffu, inc, 31);
     }
 }
+
+#endif
 
 // ORs the bits of a field into word `w`.  The field covers global bits
 // [s, s+nb) with its least significant bit last; the word covers [w0, w0+64).
