@@ -348,7 +348,7 @@ def main():
     # serial-chain parse took that place from the radix pass, the sort pass follows in "roofline_others".
     traffic = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_v13_traffic.json")))
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_v15_traffic.json")))
     except (OSError, ValueError):
         pass
 
