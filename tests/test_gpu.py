@@ -293,6 +293,31 @@ def test_host_library_encode_roundtrip(orc):
     assert lib.salz_encode_safe(b"12345678", 8, C.create_string_buffer(100), C.byref(n)) == -1
 
 
+def test_host_library_concurrent_callers(orc):
+    """salz_encode_safe from several threads at once on different buffers (the reference is
+    re-entrant, ref lib/salz.c:777-823 keeps everything in a per-call ctx; this library
+    serialises the callers on its process-wide CUDA context): every caller gets its own
+    block's bytes."""
+    from concurrent.futures import ThreadPoolExecutor
+    lib = _host_lib()
+    inputs = [synth.english_like(200000 + 1000 * i, seed=10 + i).tobytes() for i in range(4)]
+    inputs += [synth.dna_like(150000, seed=20, block=150000).tobytes(), bytes(70000), b"abcdefghi" * 3]
+    want = [orc.encode(d) for d in inputs]
+
+    def one(d):
+        cap = salz_b200.encoded_len_max(len(d))
+        dst = C.create_string_buffer(cap)
+        n = C.c_size_t(cap)
+        rc = lib.salz_encode_safe(d, len(d), dst, C.byref(n))   # ctypes drops the GIL for the call
+        return rc, dst.raw[: n.value]
+
+    for _ in range(3):
+        with ThreadPoolExecutor(len(inputs)) as ex:
+            got = list(ex.map(one, inputs))
+        for (rc, out), w in zip(got, want):
+            assert rc == 0 and out == w
+
+
 def _stream_properties(orc, data, bl, sample):
     """Size-independent checks of a whole stream: every record decodes back to its block
     (host decoder), the sizes add up to the stream, sampled blocks equal the oracle's bytes."""
