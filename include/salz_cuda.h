@@ -105,14 +105,15 @@ int salz_cuda_encode_stream_device(salz_cuda_ctx *ctx, const uint8_t *d_src,
  * to host arrays (any may be NULL):
  *   sa[n]      suffix array of src[0..n)                 (ref lib/salz.c:463-469)
  *   plcp[n], lcp[n]                                      (ref libsais.h:319,329)
+ *   psvnsv[2n] (PSV, NSV) text positions, -1 = none      (ref lib/salz.c:471-490)
  *   cand[4n]   (p-psv, psv_len, p-nsv, nsv_len)          (ref lib/salz.c:540-560)
  *   parse[3n]  (offs, len, cost) after the optimal parse (ref lib/salz.c:610-662)
  *   dst/dst_len encoded block
  */
 int salz_cuda_debug_stages(salz_cuda_ctx *ctx, const uint8_t *src, size_t N,
                            int32_t *sa, int32_t *plcp, int32_t *lcp,
-                           int32_t *cand, int32_t *parse, uint8_t *dst,
-                           size_t *dst_len);
+                           int32_t *psvnsv, int32_t *cand, int32_t *parse,
+                           uint8_t *dst, size_t *dst_len);
 
 /* Suffix arrays only, for a batch of texts laid out at `stride` bytes in one
  * host buffer (SA-build GB/s measurements).  sa_out[i*stride + r]. */
@@ -147,6 +148,61 @@ void salz_cuda_set_parse_segments(salz_cuda_ctx *ctx, int k);
  * (a cudaStream_t passed as void *; NULL restores the context's own stream),
  * so that events the caller records on that stream bracket the work. */
 void salz_cuda_set_stream(salz_cuda_ctx *ctx, void *stream);
+
+/* ---- multi-GPU: blocks sharded over the GPUs of one box -------------
+ *
+ * Replaces nothing in the reference (it is single-threaded); the unit that is
+ * sharded is the independent block of its CLI loop (ref programs/salzcli.c:143-179,
+ * context per call: ref lib/salz.c:788,821).  Rank r of `world` encodes the contiguous
+ * block range salz_cuda_block_range(nblocks, r, world) with its own salz_cuda_ctx; the
+ * only exchange is an NCCL all-gather of the per-block encoded sizes, after which every
+ * rank scans them into record offsets (framing: ref programs/salzcli.c:162-169).
+ * NCCL is bound at run time (libnccl.so.2); without it these calls fail with -1 / NULL
+ * and everything above keeps working. */
+
+#define SALZ_CUDA_UNIQUE_ID_BYTES 128
+
+typedef struct salz_cuda_comm salz_cuda_comm;
+typedef struct salz_cuda_multi salz_cuda_multi;
+
+/* [lo, hi) of the `nblocks` blocks that rank `rank` of `world` encodes. */
+void salz_cuda_block_range(size_t nblocks, int rank, int world, size_t *lo, size_t *hi);
+
+/* One rank per caller (a process or a thread per GPU).  Rank 0 makes the id
+ * (ncclGetUniqueId) and ships it to the others by whatever means the launcher
+ * has; comm_create blocks until all `world` ranks have joined. */
+int salz_cuda_comm_unique_id(uint8_t id[SALZ_CUDA_UNIQUE_ID_BYTES]);
+salz_cuda_comm *salz_cuda_comm_create(int device, const uint8_t id[SALZ_CUDA_UNIQUE_ID_BYTES],
+                                      int rank, int world);
+void salz_cuda_comm_destroy(salz_cuda_comm *comm);
+int salz_cuda_comm_rank(const salz_cuda_comm *comm);
+int salz_cuda_comm_world(const salz_cuda_comm *comm);
+uint64_t salz_cuda_comm_gathers(const salz_cuda_comm *comm);   /* all-gathers executed */
+
+/* Collective: every rank passes the encoded sizes of its own block range
+ * (nlocal must equal the length of that range); all ranks receive the sizes of
+ * all `nblocks_total` blocks in stream order and, if record_offsets != NULL, the
+ * byte offset of every record (u32 length + block) in the assembled stream,
+ * nblocks_total + 1 entries, the last being the stream length.  The 8-byte file
+ * header is the caller's, as in salz_cuda_encode_stream. */
+int salz_cuda_comm_allgather_sizes(salz_cuda_comm *comm, const uint32_t *local_sizes,
+                                   size_t nlocal, size_t nblocks_total,
+                                   uint32_t *all_sizes, uint64_t *record_offsets);
+
+/* One process driving `ndev` devices (devices == NULL: 0..ndev-1; ndev <= 0: all
+ * visible): a host thread, a salz_cuda_ctx and an NCCL rank per device. */
+salz_cuda_multi *salz_cuda_multi_create(const int *devices, int ndev,
+                                        size_t max_block_len, size_t max_batch_blocks);
+void salz_cuda_multi_destroy(salz_cuda_multi *m);
+int salz_cuda_multi_devices(const salz_cuda_multi *m);
+salz_cuda_ctx *salz_cuda_multi_ctx(salz_cuda_multi *m, int i);   /* rank i's context (stats) */
+const char *salz_cuda_multi_last_error(const salz_cuda_multi *m);
+
+/* salz_cuda_encode_stream over all devices of `m`: same arguments, same bytes. */
+int salz_cuda_multi_encode_stream(salz_cuda_multi *m, const uint8_t *src,
+                                  size_t src_len, size_t block_len, uint8_t *dst,
+                                  size_t dst_cap, size_t *dst_len,
+                                  uint32_t *block_sizes, size_t *nblocks);
 
 #ifdef __cplusplus
 }

@@ -27,7 +27,20 @@ static void drop_ctx(void)
     if (g_ctx) {
         salz_cuda_ctx_destroy(g_ctx);
         g_ctx = NULL;
+        g_ctx_block = 0;
     }
+}
+
+/* Releases the process-wide encoder context (device workspace, pinned buffers).
+ * Not part of the reference API: a host application that wants the memory back
+ * before exit calls it; the next salz_encode_safe creates a fresh context.
+ * Nothing is torn down at exit: by then the CUDA runtime's own exit handler
+ * may already have run, and the driver reclaims everything anyway. */
+void salz_shutdown(void)
+{
+    pthread_mutex_lock(&g_lock);
+    drop_ctx();
+    pthread_mutex_unlock(&g_lock);
 }
 
 int salz_encode_safe(const uint8_t *src, size_t src_len, uint8_t *dst, size_t *dst_len)
@@ -45,8 +58,6 @@ int salz_encode_safe(const uint8_t *src, size_t src_len, uint8_t *dst, size_t *d
         while (cap < src_len)
             cap <<= 1;
         const char *dev = getenv("SALZ_CUDA_DEVICE");
-        if (g_ctx == NULL)
-            atexit(drop_ctx);
         drop_ctx();
         g_ctx = salz_cuda_ctx_create(dev ? atoi(dev) : 0, cap, 1);
         g_ctx_block = g_ctx ? cap : 0;

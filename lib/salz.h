@@ -41,6 +41,10 @@ extern int salz_decode_safe(const uint8_t *src, size_t src_len, uint8_t *dst,
 extern size_t encode_vnibble_le(uint32_t val, uint64_t *res);
 extern size_t vnibble_size(uint32_t val);
 
+/* Not in the reference: releases the process-wide GPU context that
+ * salz_encode_safe creates lazily (device workspace and pinned buffers). */
+extern void salz_shutdown(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,11 +11,14 @@
  * Container: u32 magic 0x53414C5A, u32 block size, then the records
  * (reference programs/salzcli.c:115-121,162-169).
  *
- * Environment: SALZ_CUDA_DEVICE (default 0), SALZ_BATCH_MIB (default 64).
+ * Not in the reference: --gpus N (first N devices, 0 = all visible).
+ * Environment: SALZ_CUDA_DEVICE (default 0), SALZ_CUDA_DEVICES (count or a,b,c
+ * list), SALZ_BATCH_MIB (per-GPU batch, default 256).
  */
 #include <errno.h>
 #include <getopt.h>
 #include <limits.h>
+#include <pthread.h>
 #include <stdbool.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -38,6 +41,7 @@ static int verbosity = VERBOSE_INFO;
 static bool force_overwrite;
 static bool keep_source;
 static int level = 5;
+static int gpus_opt = -1;   /* --gpus N: first N devices, 0 = all; -1 = not given */
 
 #define say(lvl, ...)                      \
     do {                                   \
@@ -75,67 +79,289 @@ static void derive_outpath(const char *path, char out[PATH_MAX])
     out[keep + slen] = '\0';
 }
 
-static int do_compress(FILE *in, FILE *out)
-{
-    const uint32_t block_len = 1u << (15 + level);
-    const uint32_t magic = SALZ_MAGIC;
-    const char *env = getenv("SALZ_BATCH_MIB");
-    size_t batch_bytes = (size_t)(env ? atoi(env) : 64) << 20;
-    if (batch_bytes < block_len)
-        batch_bytes = block_len;
-    const size_t batch_blocks = batch_bytes / block_len;
-    batch_bytes = batch_blocks * block_len;
-    const size_t out_cap = batch_blocks * ((size_t)salz_encoded_len_max(block_len) + 4);
-    env = getenv("SALZ_CUDA_DEVICE");
+/* ---- compress: reader -> GPU(s) -> writer -------------------------------------
+ * The reference reads a block, encodes it and writes it, one after the other
+ * (reference programs/salzcli.c:143-179).  Here three threads share a ring of
+ * NSLOT pinned buffer pairs: the reader fills slot i+1 and the writer drains
+ * slot i-1 while the encoder (this thread) has slot i on the GPUs, so file I/O
+ * runs under the kernels.  A slot holds `gpus x per-GPU batch` blocks; the
+ * multi-GPU entry cuts it into one contiguous block range per device and
+ * assembles the records after the NCCL all-gather of their sizes.  The encoder
+ * context (device workspaces, NCCL ranks) is created once per process. */
+#define NSLOT 3
 
-    int rc = -1;
-    uint8_t *inbuf = NULL, *outbuf = NULL;
-    salz_cuda_ctx *ctx = salz_cuda_ctx_create(env ? atoi(env) : 0, block_len, batch_blocks);
-    if (ctx == NULL) {
-        say(QUIET_ERR, "Couldn't create CUDA encoder context (no GPU?)");
-        return -1;
+enum { SLOT_FREE, SLOT_FILLED, SLOT_ENCODED };
+
+struct slot {
+    uint8_t *in, *out;
+    size_t got, produced;
+    bool last;
+    int state;
+};
+
+struct pipe_ctx {
+    FILE *in, *out;
+    struct slot slot[NSLOT];
+    size_t batch_bytes, block_len;
+    pthread_mutex_t mu;
+    pthread_cond_t cv;
+    bool failed;          /* any stage failed: everybody drains and leaves */
+    const char *why;      /* message of the first failure */
+};
+
+static void pipe_fail(struct pipe_ctx *p, const char *why)
+{
+    pthread_mutex_lock(&p->mu);
+    if (!p->failed) {
+        p->failed = true;
+        p->why = why;
     }
-    inbuf = salz_cuda_host_alloc(batch_bytes);
-    outbuf = salz_cuda_host_alloc(out_cap);
-    if (inbuf == NULL || outbuf == NULL) {
-        say(QUIET_ERR, "Couldn't allocate memory: (%zu bytes)", batch_bytes + out_cap);
-        goto done;
-    }
-    if (fwrite(&magic, 1, 4, out) != 4 || fwrite(&block_len, 1, 4, out) != 4) {
-        say(QUIET_ERR, "Couldn't write SALZ header to output");
-        goto done;
-    }
-    for (;;) {
-        size_t got = fread(inbuf, 1, batch_bytes, in);
-        if (got != batch_bytes && ferror(in)) {
-            say(QUIET_ERR, "Couldn't read from input stream");
-            goto done;
+    pthread_cond_broadcast(&p->cv);
+    pthread_mutex_unlock(&p->mu);
+}
+
+static void *reader_main(void *arg)
+{
+    struct pipe_ctx *p = arg;
+    for (int i = 0;; i = (i + 1) % NSLOT) {
+        struct slot *s = &p->slot[i];
+        pthread_mutex_lock(&p->mu);
+        while (s->state != SLOT_FREE && !p->failed)
+            pthread_cond_wait(&p->cv, &p->mu);
+        const bool stop = p->failed;
+        pthread_mutex_unlock(&p->mu);
+        if (stop)
+            break;
+        const size_t got = fread(s->in, 1, p->batch_bytes, p->in);
+        if (got != p->batch_bytes && ferror(p->in)) {
+            pipe_fail(p, "Couldn't read from input stream");
+            break;
         }
         /* The reference encodes one more (short or empty) block after every
          * full-size read, so a file whose size is a multiple of the block size,
          * or whose tail is <= 8 bytes, fails there; keep that behaviour. */
-        const bool last = got != batch_bytes;
-        if (got == 0 || (last && got % block_len == 0)) {
-            say(QUIET_ERR, "Couldn't encode segment");
-            goto done;
+        const bool last = got != p->batch_bytes;
+        if (got == 0 || (last && got % p->block_len == 0)) {
+            pipe_fail(p, "Couldn't encode segment");
+            break;
         }
-        size_t produced = 0;
-        if (salz_cuda_encode_stream(ctx, inbuf, got, block_len, outbuf, out_cap, &produced, NULL, NULL) != 0) {
-            say(QUIET_ERR, "Couldn't encode segment");
-            goto done;
-        }
-        if (fwrite(outbuf, 1, produced, out) != produced) {
-            say(QUIET_ERR, "Couldn't write encoded segment to output stream");
-            goto done;
-        }
+        pthread_mutex_lock(&p->mu);
+        s->got = got;
+        s->last = last;
+        s->state = SLOT_FILLED;
+        pthread_cond_broadcast(&p->cv);
+        pthread_mutex_unlock(&p->mu);
         if (last)
             break;
     }
-    rc = 0;
+    return NULL;
+}
+
+static void *writer_main(void *arg)
+{
+    struct pipe_ctx *p = arg;
+    for (int i = 0;; i = (i + 1) % NSLOT) {
+        struct slot *s = &p->slot[i];
+        pthread_mutex_lock(&p->mu);
+        while (s->state != SLOT_ENCODED && !p->failed)
+            pthread_cond_wait(&p->cv, &p->mu);
+        const bool stop = p->failed;
+        pthread_mutex_unlock(&p->mu);
+        if (stop)
+            break;
+        if (fwrite(s->out, 1, s->produced, p->out) != s->produced) {
+            pipe_fail(p, "Couldn't write encoded segment to output stream");
+            break;
+        }
+        const bool last = s->last;
+        pthread_mutex_lock(&p->mu);
+        s->state = SLOT_FREE;
+        pthread_cond_broadcast(&p->cv);
+        pthread_mutex_unlock(&p->mu);
+        if (last)
+            break;
+    }
+    return NULL;
+}
+
+/* Encoder context of the process: created by the first file, reused by the rest. */
+static salz_cuda_multi *g_enc;
+static uint8_t *g_in[NSLOT], *g_out[NSLOT];
+static size_t g_batch_bytes, g_out_cap;
+
+static void encoder_release(void)
+{
+    for (int i = 0; i < NSLOT; i++) {
+        salz_cuda_host_free(g_in[i]);
+        salz_cuda_host_free(g_out[i]);
+        g_in[i] = g_out[i] = NULL;
+    }
+    salz_cuda_multi_destroy(g_enc);
+    g_enc = NULL;
+}
+
+/* Devices: --gpus N / SALZ_CUDA_DEVICES=N (first N devices, 0 = all) or
+ * SALZ_CUDA_DEVICES=a,b,c (that list); default: SALZ_CUDA_DEVICE or device 0. */
+static int pick_devices(int devs[64])
+{
+    const char *list = getenv("SALZ_CUDA_DEVICES");
+    const int have = salz_cuda_device_count();
+    int n = 0;
+    if (gpus_opt >= 0) {
+        n = gpus_opt == 0 ? have : gpus_opt;
+        for (int i = 0; i < n && i < 64; i++)
+            devs[i] = i;
+    } else if (list && strchr(list, ',')) {
+        char tmp[256];
+        snprintf(tmp, sizeof(tmp), "%s", list);
+        for (char *t = strtok(tmp, ","); t && n < 64; t = strtok(NULL, ","))
+            devs[n++] = atoi(t);
+    } else if (list) {
+        n = atoi(list) == 0 ? have : atoi(list);
+        for (int i = 0; i < n && i < 64; i++)
+            devs[i] = i;
+    } else {
+        const char *one = getenv("SALZ_CUDA_DEVICE");
+        devs[0] = one ? atoi(one) : 0;
+        n = 1;
+    }
+    return n > 64 ? 64 : n;
+}
+
+static int encoder_acquire(size_t block_len, size_t file_size)
+{
+    if (g_enc != NULL)
+        return 0;
+    int devs[64];
+    const int ndev = pick_devices(devs);
+    if (ndev <= 0) {
+        say(QUIET_ERR, "Couldn't create CUDA encoder context (no GPU?)");
+        return -1;
+    }
+    /* Per-GPU batch: large enough to fill the device (default 256 MiB: ~23 GB of
+     * workspace), no larger than this file's share of blocks needs. */
+    const char *env = getenv("SALZ_BATCH_MIB");
+    size_t per_gpu = (size_t)(env ? atoi(env) : 256) << 20;
+    if (per_gpu < block_len)
+        per_gpu = block_len;
+    size_t blocks = per_gpu / block_len;
+    const size_t file_blocks = file_size / block_len + 1;
+    const size_t share = divup(file_blocks, (size_t)ndev);
+    if (blocks > share)
+        blocks = share;
+    if (blocks > 65535)
+        blocks = 65535;
+    g_enc = salz_cuda_multi_create(devs, ndev, block_len, blocks);
+    if (g_enc == NULL) {
+        say(QUIET_ERR, "Couldn't create CUDA encoder context (no GPU?)");
+        return -1;
+    }
+    g_batch_bytes = blocks * block_len * (size_t)ndev;
+    g_out_cap = blocks * (size_t)ndev * ((size_t)salz_encoded_len_max(block_len) + 4);
+    /* a file that fits one slot needs one buffer pair only */
+    const int nslot = file_size < g_batch_bytes ? 1 : NSLOT;
+    for (int i = 0; i < nslot; i++) {
+        g_in[i] = salz_cuda_host_alloc(g_batch_bytes);
+        g_out[i] = salz_cuda_host_alloc(g_out_cap);
+        if (g_in[i] == NULL || g_out[i] == NULL) {
+            say(QUIET_ERR, "Couldn't allocate memory: (%zu bytes)", g_batch_bytes + g_out_cap);
+            encoder_release();
+            return -1;
+        }
+    }
+    return 0;
+}
+
+static int do_compress(FILE *in, FILE *out, size_t file_size)
+{
+    const uint32_t block_len = 1u << (15 + level);
+    const uint32_t magic = SALZ_MAGIC;
+    if (encoder_acquire(block_len, file_size) != 0)
+        return -1;
+    const int want = file_size < g_batch_bytes ? 1 : NSLOT;   /* a later, larger file: all slots */
+    for (int i = 0; i < want; i++)
+        if (g_in[i] == NULL || g_out[i] == NULL) {
+            if (g_in[i] == NULL)
+                g_in[i] = salz_cuda_host_alloc(g_batch_bytes);
+            if (g_out[i] == NULL)
+                g_out[i] = salz_cuda_host_alloc(g_out_cap);
+            if (g_in[i] == NULL || g_out[i] == NULL) {
+                say(QUIET_ERR, "Couldn't allocate memory: (%zu bytes)", g_batch_bytes + g_out_cap);
+                return -1;
+            }
+        }
+    if (fwrite(&magic, 1, 4, out) != 4 || fwrite(&block_len, 1, 4, out) != 4) {
+        say(QUIET_ERR, "Couldn't write SALZ header to output");
+        return -1;
+    }
+    struct pipe_ctx p;
+    memset(&p, 0, sizeof(p));
+    p.in = in;
+    p.out = out;
+    p.batch_bytes = g_batch_bytes;
+    p.block_len = block_len;
+    pthread_mutex_init(&p.mu, NULL);
+    pthread_cond_init(&p.cv, NULL);
+    int nslot = 0;
+    for (int i = 0; i < NSLOT && g_in[i] && g_out[i]; i++) {
+        p.slot[i].in = g_in[i];
+        p.slot[i].out = g_out[i];
+        p.slot[i].state = SLOT_FREE;
+        nslot++;
+    }
+    int rc = -1;
+    if (nslot < NSLOT) {
+        /* one slot: the file fits it; nothing to overlap */
+        struct slot *s = &p.slot[0];
+        s->got = fread(s->in, 1, p.batch_bytes, in);
+        if (s->got != p.batch_bytes && ferror(in)) {
+            say(QUIET_ERR, "Couldn't read from input stream");
+        } else if (s->got == 0 || s->got % block_len == 0 || s->got == p.batch_bytes) {
+            say(QUIET_ERR, "Couldn't encode segment");
+        } else if (salz_cuda_multi_encode_stream(g_enc, s->in, s->got, block_len, s->out, g_out_cap, &s->produced, NULL,
+                                                 NULL) != 0) {
+            say(QUIET_ERR, "Couldn't encode segment");
+        } else if (fwrite(s->out, 1, s->produced, out) != s->produced) {
+            say(QUIET_ERR, "Couldn't write encoded segment to output stream");
+        } else {
+            rc = 0;
+        }
+        goto done;
+    }
+    pthread_t rd, wr;
+    pthread_create(&rd, NULL, reader_main, &p);
+    pthread_create(&wr, NULL, writer_main, &p);
+    for (int i = 0;; i = (i + 1) % NSLOT) {
+        struct slot *s = &p.slot[i];
+        pthread_mutex_lock(&p.mu);
+        while (s->state != SLOT_FILLED && !p.failed)
+            pthread_cond_wait(&p.cv, &p.mu);
+        const bool stop = p.failed;
+        pthread_mutex_unlock(&p.mu);
+        if (stop)
+            break;
+        if (salz_cuda_multi_encode_stream(g_enc, s->in, s->got, block_len, s->out, g_out_cap, &s->produced, NULL,
+                                          NULL) != 0) {
+            pipe_fail(&p, "Couldn't encode segment");
+            break;
+        }
+        const bool last = s->last;
+        pthread_mutex_lock(&p.mu);
+        s->state = SLOT_ENCODED;
+        pthread_cond_broadcast(&p.cv);
+        pthread_mutex_unlock(&p.mu);
+        if (last)
+            break;
+    }
+    pthread_join(rd, NULL);
+    pthread_join(wr, NULL);
+    if (p.failed)
+        say(QUIET_ERR, "%s", p.why);
+    else
+        rc = 0;
 done:
-    salz_cuda_host_free(inbuf);
-    salz_cuda_host_free(outbuf);
-    salz_cuda_ctx_destroy(ctx);
+    pthread_mutex_destroy(&p.mu);
+    pthread_cond_destroy(&p.cv);
     return rc;
 }
 
@@ -243,7 +469,7 @@ static int handle_file(const char *path)
 
     uint64_t t0 = 0, t1 = 0;
     get_time_ns(&t0);
-    int rc = (mode == MODE_COMPRESS) ? do_compress(in, out) : do_decompress(in, out);
+    int rc = (mode == MODE_COMPRESS) ? do_compress(in, out, (size_t)in_size) : do_decompress(in, out);
     get_time_ns(&t1);
     fclose(out);
     fclose(in);
@@ -283,7 +509,8 @@ static void usage(const char *name)
            "  -0 ... -9          compression level [default: 5]\n"
            "                     (note that memory usage grows exponentially)\n"
            "  --fast             alias of \"-1\"\n"
-           "  --best             alias of \"-9\"\n\n"
+           "  --best             alias of \"-9\"\n"
+           "  --gpus N           compress on the first N GPUs (0 = all) [default: 1]\n\n"
            "  Default action is to compress.\n"
            "  If invoked as \"unsalz\", default action is to decompress.\n"
            "                \"salzcat\", default action is to decompress to stdout.\n\n"
@@ -299,7 +526,8 @@ int main(int argc, char *argv[])
         { "force", no_argument, NULL, 'f' },      { "help", no_argument, NULL, 'h' },
         { "keep", no_argument, NULL, 'k' },       { "list", no_argument, NULL, 'l' },
         { "quiet", no_argument, NULL, 'q' },      { "fast", no_argument, NULL, '1' },
-        { "best", no_argument, NULL, '9' },       { NULL, 0, NULL, 0 },
+        { "best", no_argument, NULL, '9' },       { "gpus", required_argument, NULL, 'G' },
+        { NULL, 0, NULL, 0 },
     };
     const char *self = base_name(argv[0]);
     int opt;
@@ -312,6 +540,9 @@ int main(int argc, char *argv[])
         case 'c':
             fprintf(stderr, "writing to stdout not supported\n");
             return -1;
+        case 'G':
+            gpus_opt = atoi(optarg);
+            break;
         case 'd':
             mode = MODE_DECOMPRESS;
             break;
@@ -351,5 +582,6 @@ int main(int argc, char *argv[])
         int rc = handle_file(argv[i]);
         worst = min(worst, rc);
     }
+    encoder_release();
     return worst;
 }

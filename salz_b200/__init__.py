@@ -7,6 +7,8 @@ without a CUDA device every call raises.
 """
 from .api import (  # noqa: F401
     SalzCuda,
+    SalzCudaMulti,
+    ShardComm,
     SalzCudaError,
     encoded_len_max,
     load_library,
@@ -14,4 +16,4 @@ from .api import (  # noqa: F401
     frame_file,
 )
 
-__all__ = ["SalzCuda", "SalzCudaError", "encoded_len_max", "load_library", "SALZ_MAGIC", "frame_file"]
+__all__ = ["SalzCuda", "SalzCudaMulti", "ShardComm", "SalzCudaError", "encoded_len_max", "load_library", "SALZ_MAGIC", "frame_file"]

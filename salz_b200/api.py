@@ -19,7 +19,13 @@ EXPORTS = [
     "salz_cuda_encode_blocks", "salz_cuda_encode_stream", "salz_cuda_encode_stream_device",
     "salz_cuda_debug_stages", "salz_cuda_suffix_arrays", "salz_cuda_get_stats", "salz_cuda_reset_stats",
     "salz_cuda_set_sort_mode", "salz_cuda_set_parse_segments", "salz_cuda_host_alloc", "salz_cuda_host_free", "salz_cuda_set_stream",
+    # multi-GPU (csrc/multi_gpu.cu)
+    "salz_cuda_block_range", "salz_cuda_comm_unique_id", "salz_cuda_comm_create", "salz_cuda_comm_destroy",
+    "salz_cuda_comm_rank", "salz_cuda_comm_world", "salz_cuda_comm_gathers", "salz_cuda_comm_allgather_sizes",
+    "salz_cuda_multi_create", "salz_cuda_multi_destroy", "salz_cuda_multi_devices", "salz_cuda_multi_ctx",
+    "salz_cuda_multi_last_error", "salz_cuda_multi_encode_stream",
 ]
+UNIQUE_ID_BYTES = 128
 
 
 class SalzCudaError(RuntimeError):
@@ -60,7 +66,7 @@ def load_library():
     L.salz_cuda_encode_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_size_t,
                                           szp, u32p, szp]
     L.salz_cuda_encode_stream_device.argtypes = L.salz_cuda_encode_stream.argtypes
-    L.salz_cuda_debug_stages.argtypes = [C.c_void_p, u8p, C.c_size_t, i32p, i32p, i32p, i32p, i32p, u8p, szp]
+    L.salz_cuda_debug_stages.argtypes = [C.c_void_p, u8p, C.c_size_t, i32p, i32p, i32p, i32p, i32p, i32p, u8p, szp]
     L.salz_cuda_suffix_arrays.argtypes = [C.c_void_p, u8p, u32p, C.c_size_t, C.c_size_t, i32p]
     L.salz_cuda_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.salz_cuda_reset_stats.argtypes = [C.c_void_p]
@@ -70,8 +76,142 @@ def load_library():
     L.salz_cuda_host_alloc.restype = C.c_void_p
     L.salz_cuda_host_alloc.argtypes = [C.c_size_t]
     L.salz_cuda_host_free.argtypes = [C.c_void_p]
+    u64p = C.POINTER(C.c_uint64)
+    L.salz_cuda_block_range.restype = None
+    L.salz_cuda_block_range.argtypes = [C.c_size_t, C.c_int, C.c_int, szp, szp]
+    L.salz_cuda_comm_unique_id.argtypes = [u8p]
+    L.salz_cuda_comm_create.restype = C.c_void_p
+    L.salz_cuda_comm_create.argtypes = [C.c_int, u8p, C.c_int, C.c_int]
+    L.salz_cuda_comm_destroy.argtypes = [C.c_void_p]
+    L.salz_cuda_comm_rank.argtypes = [C.c_void_p]
+    L.salz_cuda_comm_world.argtypes = [C.c_void_p]
+    L.salz_cuda_comm_gathers.restype = C.c_uint64
+    L.salz_cuda_comm_gathers.argtypes = [C.c_void_p]
+    L.salz_cuda_comm_allgather_sizes.argtypes = [C.c_void_p, u32p, C.c_size_t, C.c_size_t, u32p, u64p]
+    L.salz_cuda_multi_create.restype = C.c_void_p
+    L.salz_cuda_multi_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_size_t, C.c_size_t]
+    L.salz_cuda_multi_destroy.argtypes = [C.c_void_p]
+    L.salz_cuda_multi_devices.argtypes = [C.c_void_p]
+    L.salz_cuda_multi_ctx.restype = C.c_void_p
+    L.salz_cuda_multi_ctx.argtypes = [C.c_void_p, C.c_int]
+    L.salz_cuda_multi_last_error.restype = C.c_char_p
+    L.salz_cuda_multi_last_error.argtypes = [C.c_void_p]
+    L.salz_cuda_multi_encode_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p, C.c_size_t,
+                                                szp, u32p, szp]
     _lib = L
     return L
+
+
+def block_range(nblocks, rank, world):
+    """[lo, hi) of the blocks rank `rank` of `world` encodes (salz_cuda_block_range)."""
+    lo, hi = C.c_size_t(0), C.c_size_t(0)
+    load_library().salz_cuda_block_range(nblocks, rank, world, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
+
+
+def _preload_nccl():
+    """The C library binds NCCL by soname at run time (dlopen "libnccl.so.2").  In a Python
+    process that also imports torch, load the copy bundled with PyTorch first so that both
+    end up on ONE NCCL (the process must not hold two versions under the same soname)."""
+    global _nccl_preloaded
+    if _nccl_preloaded:
+        return
+    _nccl_preloaded = True
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia")
+        for base in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(base, "nccl", "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+                return
+    except (OSError, ImportError, AttributeError):
+        pass
+
+
+_nccl_preloaded = False
+
+
+def unique_id():
+    """128-byte NCCL id made by rank 0 and shipped to the other ranks by the launcher."""
+    _preload_nccl()
+    buf = (C.c_uint8 * UNIQUE_ID_BYTES)()
+    if load_library().salz_cuda_comm_unique_id(buf) != 0:
+        raise SalzCudaError("salz_cuda_comm_unique_id failed (NCCL missing?)")
+    return bytes(buf)
+
+
+class ShardComm:
+    """One rank of the size all-gather (NCCL, bound by the C library): include/salz_cuda.h."""
+
+    def __init__(self, device, uid, rank, world):
+        self.lib = load_library()
+        _preload_nccl()
+        buf = (C.c_uint8 * UNIQUE_ID_BYTES).from_buffer_copy(uid)
+        self.h = self.lib.salz_cuda_comm_create(device, buf, rank, world)
+        if not self.h:
+            raise SalzCudaError("salz_cuda_comm_create failed")
+        self.rank, self.world = rank, world
+
+    def allgather_sizes(self, local_sizes, nblocks_total):
+        """-> (sizes of all blocks, record offsets [nblocks_total + 1]); collective."""
+        mine = np.ascontiguousarray(local_sizes, dtype=np.uint32)
+        sizes = np.zeros(nblocks_total, np.uint32)
+        offs = np.zeros(nblocks_total + 1, np.uint64)
+        rc = self.lib.salz_cuda_comm_allgather_sizes(self.h, mine.ctypes.data_as(u32p), len(mine), nblocks_total,
+                                                     sizes.ctypes.data_as(u32p),
+                                                     offs.ctypes.data_as(C.POINTER(C.c_uint64)))
+        if rc != 0:
+            raise SalzCudaError("salz_cuda_comm_allgather_sizes failed")
+        return sizes, offs
+
+    def gathers(self):
+        return int(self.lib.salz_cuda_comm_gathers(self.h))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.salz_cuda_comm_destroy(self.h)
+            self.h = None
+
+
+class SalzCudaMulti:
+    """One process, several GPUs: salz_cuda_multi_* (a thread, a context and an NCCL rank per device)."""
+
+    def __init__(self, ndev=0, max_block_len=1 << 20, max_batch_blocks=64, devices=None):
+        self.lib = load_library()
+        _preload_nccl()
+        arr = (C.c_int * len(devices))(*devices) if devices else None
+        self.h = self.lib.salz_cuda_multi_create(arr, len(devices) if devices else ndev, max_block_len, max_batch_blocks)
+        if not self.h:
+            raise SalzCudaError("salz_cuda_multi_create failed")
+        self.ndev = self.lib.salz_cuda_multi_devices(self.h)
+
+    def encode_stream(self, data, block_len):
+        src = _u8(data)
+        cap = stream_len_max(len(src), block_len)
+        dst = np.empty(cap, np.uint8)
+        nb = (len(src) + block_len - 1) // block_len
+        sizes = np.zeros(nb, np.uint32)
+        dl, nbo = C.c_size_t(0), C.c_size_t(0)
+        rc = self.lib.salz_cuda_multi_encode_stream(self.h, src.ctypes.data, len(src), block_len, dst.ctypes.data, cap,
+                                                    C.byref(dl), sizes.ctypes.data_as(u32p), C.byref(nbo))
+        if rc != 0:
+            raise SalzCudaError(self.lib.salz_cuda_multi_last_error(self.h).decode())
+        return dst[: dl.value].tobytes(), sizes
+
+    def encode_stream_ptr(self, src_ptr, src_len, block_len, dst_ptr, dst_cap, sizes=None):
+        dl, nbo = C.c_size_t(0), C.c_size_t(0)
+        sp = sizes.ctypes.data_as(u32p) if sizes is not None else None
+        rc = self.lib.salz_cuda_multi_encode_stream(self.h, src_ptr, src_len, block_len, dst_ptr, dst_cap,
+                                                    C.byref(dl), sp, C.byref(nbo))
+        if rc != 0:
+            raise SalzCudaError(self.lib.salz_cuda_multi_last_error(self.h).decode())
+        return dl.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.salz_cuda_multi_destroy(self.h)
+            self.h = None
 
 
 def encoded_len_max(n):
@@ -199,16 +339,16 @@ class SalzCuda:
         N = len(src)
         n = N - 8
         sa = np.zeros(n, np.int32); plcp = np.zeros(n, np.int32); lcp = np.zeros(n, np.int32)
-        cand = np.zeros((n, 4), np.int32); parse = np.zeros((n, 3), np.int32)
+        cand = np.zeros((n, 4), np.int32); parse = np.zeros((n, 3), np.int32); pn = np.zeros((n, 2), np.int32)
         cap = encoded_len_max(N)
         dst = np.zeros(cap, np.uint8); dl = C.c_size_t(cap)
         rc = self.lib.salz_cuda_debug_stages(
             self.ctx, src.ctypes.data_as(u8p), N, sa.ctypes.data_as(i32p), plcp.ctypes.data_as(i32p),
-            lcp.ctypes.data_as(i32p), cand.ctypes.data_as(i32p), parse.ctypes.data_as(i32p),
-            dst.ctypes.data_as(u8p), C.byref(dl))
+            lcp.ctypes.data_as(i32p), pn.ctypes.data_as(i32p), cand.ctypes.data_as(i32p),
+            parse.ctypes.data_as(i32p), dst.ctypes.data_as(u8p), C.byref(dl))
         if rc != 0:
             raise SalzCudaError(self._err())
-        return dict(sa=sa, plcp=plcp, lcp=lcp, cand=cand, parse=parse, out=dst[: dl.value].tobytes())
+        return dict(sa=sa, plcp=plcp, lcp=lcp, psvnsv=pn, cand=cand, parse=parse, out=dst[: dl.value].tobytes())
 
     def suffix_arrays(self, texts):
         """texts: list of bytes-like (each <= max_block_len - 8).  Returns list of int32 arrays."""

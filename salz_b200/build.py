@@ -5,10 +5,10 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsalz_cuda.so")
-SOURCES = ["sa.cu", "lcp.cu", "ansv.cu", "parse.cu", "emit.cu", "api.cu"]
+SOURCES = ["sa.cu", "lcp.cu", "ansv.cu", "parse.cu", "emit.cu", "api.cu", "multi_gpu.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "-cudart", "static",
+    "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "-ldl",
 ]
 
 

@@ -80,7 +80,12 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
         fprintf(stderr, "salz_cuda: no CUDA device %d (found %d); there is no CPU fallback\n", device, ndev);
         return nullptr;
     }
+    if (max_batch_blocks > 65535) {  // the block index is gridDim.y of three kernels
+        fprintf(stderr, "salz_cuda: max_batch_blocks %zu exceeds 65535\n", max_batch_blocks);
+        return nullptr;
+    }
     if (cudaSetDevice(device) != cudaSuccess) return nullptr;
+    if (sa_init_device() || parse_init_device()) return nullptr;
     salz_cuda_ctx *c = new salz_cuda_ctx();
     c->device = device;
     c->maxBlockLen = max_block_len;
@@ -313,8 +318,9 @@ static int stream_common(salz_cuda_ctx *c, const uint8_t *src, bool srcOnDevice,
         // incompressible block can overflow it by < 8 bytes and the reference
         // CLI then fails the whole file (ref lib/salz.c:260,274).  Same here.
         for (int b = 0; b < B; b++) {
-            size_t N = c->h_blkN[b];
-            if (c->h_salzLen[b] > 4 + N + (N + 63) / 64 * 8) {
+            // capacity the reference CLI gives every block, the short tail block included
+            // (ref programs/salzcli.c:129: salz_encoded_len_max(plain_len))
+            if (c->h_salzLen[b] > 4 + block_len + (block_len + 63) / 64 * 8) {
                 set_err(c, "block %zu: intermediate stream exceeds salz_encoded_len_max (reference fails too)", b0 + b);
                 return -1;
             }
@@ -366,9 +372,16 @@ static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, siz
     const size_t nbatch = cut.size() - 1;
     auto batch_off = [&](size_t i) { return cut[i] * block_len; };
     auto batch_bytes = [&](size_t i) { return std::min(src_len, cut[i + 1] * block_len) - cut[i] * block_len; };
+    // on every return (errors included): no copy still reads the caller's src or writes its dst
     struct Restore {
         salz_cuda_ctx *c;
-        ~Restore() { c->ws.T = c->Tbuf[0]; c->ws.out = c->outbuf[0]; }
+        ~Restore()
+        {
+            cudaStreamSynchronize(c->copyStream);
+            cudaStreamSynchronize(c->stream);
+            c->ws.T = c->Tbuf[0];
+            c->ws.out = c->outbuf[0];
+        }
     } restore{c};
     // everything queued earlier on the compute stream is done before the buffers are reused
     CKC(c, cudaEventRecord(c->computed, st));
@@ -394,8 +407,9 @@ static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, siz
         ws.out = c->outbuf[k];
         if (run_batch(c, B, block_len, 1, 5)) return -1;
         for (int b = 0; b < B; b++) {
-            size_t N = c->h_blkN[b];
-            if (c->h_salzLen[b] > 4 + N + (N + 63) / 64 * 8) {
+            // capacity the reference CLI gives every block, the short tail block included
+            // (ref programs/salzcli.c:129: salz_encoded_len_max(plain_len))
+            if (c->h_salzLen[b] > 4 + block_len + (block_len + 63) / 64 * 8) {
                 set_err(c, "block %zu: intermediate stream exceeds salz_encoded_len_max (reference fails too)", b0 + b);
                 return -1;
             }
@@ -469,7 +483,8 @@ extern "C" int salz_cuda_encode_blocks(salz_cuda_ctx *c, const uint8_t *const *s
 }
 
 extern "C" int salz_cuda_debug_stages(salz_cuda_ctx *c, const uint8_t *src, size_t N, int32_t *sa, int32_t *plcp,
-                                      int32_t *lcp, int32_t *cand, int32_t *parse, uint8_t *dst, size_t *dst_len)
+                                      int32_t *lcp, int32_t *psvnsv, int32_t *cand, int32_t *parse, uint8_t *dst,
+                                      size_t *dst_len)
 {
     if (!c || !src || N <= 8 || N > c->ws.S) return -1;
     if (cudaSetDevice(c->device) != cudaSuccess) return -1;
@@ -483,6 +498,17 @@ extern "C" int salz_cuda_debug_stages(salz_cuda_ctx *c, const uint8_t *src, size
     if (plcp) CKC(c, cudaMemcpy(plcp, ws.plcp, n * 4, cudaMemcpyDeviceToHost));
     if (lcp) CKC(c, cudaMemcpy(lcp, ws.lcp, n * 4, cudaMemcpyDeviceToHost));
     if (cand) CKC(c, cudaMemcpy(cand, ws.cand, n * 16, cudaMemcpyDeviceToHost));
+    if (psvnsv) {
+        // the ANSV pass leaves distances (p - PSV, p - NSV; p + 1 when there is none); the
+        // reference's aux[4p+0/1] after build_psvnsv_array are the positions themselves
+        std::vector<int32_t> cd(4 * n);
+        CKC(c, cudaMemcpy(cd.data(), ws.cand, n * 16, cudaMemcpyDeviceToHost));
+        psvnsv[0] = psvnsv[1] = -1;  // nothing is smaller than position 0
+        for (size_t p = 1; p < n; p++) {
+            psvnsv[2 * p] = (int32_t)p - cd[4 * p];
+            psvnsv[2 * p + 1] = (int32_t)p - cd[4 * p + 2];
+        }
+    }
     if (parse) {
         // cost[p] (the reference's aux[4p+2]) = d[p] - 9p, d = relative value + segment base
         std::vector<int32_t> ch(2 * n), cs(n + 1), sb(64);

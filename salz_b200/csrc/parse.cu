@@ -434,14 +434,16 @@ __global__ void __launch_bounds__(256) k_choose(const int4 *__restrict__ cand, c
 
 }  // namespace
 
+// Per-device kernel attributes; called by salz_cuda_ctx_create after cudaSetDevice.
+int parse_init_device()
+{
+    if (cudaFuncSetAttribute(k_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PARSE_SMEM) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(k_parse, cudaFuncAttributePreferredSharedMemoryCarveout, 100) != cudaSuccess) return -1;
+    return 0;
+}
+
 int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc)
 {
-    static bool attrSet = false;
-    if (!attrSet) {
-        cudaFuncSetAttribute(k_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PARSE_SMEM);
-        cudaFuncSetAttribute(k_parse, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        attrSet = true;
-    }
     // Segments per block: several chains per slot (NCH chains per CTA, SALZ_PARSE_CTAS CTAs
     // per SM) so that the slots stay busy to the end of a pass, segments of at least 64 chunks (16384)
     // positions); a cut only pays when it is at least 4-fold (two passes of the chains +

@@ -1506,18 +1506,21 @@ int sa_build_pairs(SortCtx &s, int &rounds)
 
 int sa_tile_elems() { return TILE < LTILE ? TILE : LTILE; }
 
+// Per-device kernel attributes (cudaFuncSetAttribute applies to the current device only):
+// called by salz_cuda_ctx_create right after cudaSetDevice, once per context.
+int sa_init_device()
+{
+    CK(cudaFuncSetAttribute(k_scatter<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
+    CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
+    CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+    CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+    return 0;
+}
+
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st, LaunchCounter &lc,
              uint64_t &algBytes, int &rounds, float *msSort)
 {
     if (bd.M == 0) return 0;
-    static bool attrSet = false;
-    if (!attrSet) {
-        CK(cudaFuncSetAttribute(k_scatter<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
-        CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
-        CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
-        CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
-        attrSet = true;
-    }
     SortCtx s = {ws, bd, st, lc, sortMode == 0, msSort, nullptr, nullptr, 0};
     if (msSort) {
         CK(cudaEventCreate(&s.evA));

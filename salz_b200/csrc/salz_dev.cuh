@@ -148,6 +148,7 @@ struct LaunchCounter { uint64_t launches, sort_launches, sort_elems, sort_bytes;
 
 // sa.cu
 int sa_tile_elems();  // list elements per sort tile
+int sa_init_device();    // kernel attributes of the current device (per context)
 int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st,
              LaunchCounter &lc, uint64_t &algBytes, int &rounds, float *msSort);
 // lcp.cu
@@ -156,6 +157,7 @@ int pyramid_upper_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, Lau
 // ansv.cu
 int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
 // parse.cu
+int parse_init_device();
 int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter &lc);
 // emit.cu
 int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,

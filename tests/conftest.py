@@ -27,6 +27,21 @@ def ref():
 
 
 @pytest.fixture(scope="session")
+def orc():
+    """The compiled reference (oracle/_ref/libsalz_ref.so: upstream salz + libsais built by
+    oracle/Makefile).  GPU parity is pinned against it and nothing else: when the prebuilt
+    library did not travel to this box the tests FAIL - they never fall back to the
+    restatement in oracle/salz_oracle.c, which is this repository's own code."""
+    from oracle.binding import Ref
+    if not Ref.available():
+        pytest.fail("oracle/_ref/libsalz_ref.so is absent: build it where /root/reference exists "
+                    "(make -C oracle) and let it travel with the tree; refusing to check the CUDA "
+                    "path against a self-written oracle")
+    print("oracle: compiled reference (oracle/_ref/libsalz_ref.so)")
+    return Ref()
+
+
+@pytest.fixture(scope="session")
 def enc():
     """One small CUDA context shared by the GPU tests (1 MiB blocks, batches of 8)."""
     import salz_b200

@@ -72,3 +72,17 @@ def test_two_rank_assembly_matches_single_process():
         r = orc.encode(data[off: off + block_len])
         want += len(r).to_bytes(4, "little") + r
     assert bytes(out) == bytes(want)
+
+
+def test_block_range_matches_the_c_library():
+    """salz_b200/shard.py (torch.distributed tests) and salz_cuda_block_range (the C path) cut
+    the block index space the same way."""
+    from salz_b200 import api, shard
+    for nblocks in (1, 2, 7, 8, 9, 257, 8193):
+        for world in (1, 2, 3, 4, 8):
+            cover = []
+            for r in range(world):
+                assert api.block_range(nblocks, r, world) == shard.block_range(nblocks, r, world)
+                lo, hi = api.block_range(nblocks, r, world)
+                cover += list(range(lo, hi))
+            assert cover == list(range(nblocks))
