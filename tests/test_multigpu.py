@@ -84,9 +84,11 @@ def _reference_stream(orc, data, bl):
 
 def _mixed(bl, nblocks, tail=4321):
     from salz_b200 import synth
-    k = max(1, nblocks // 4)
+    if nblocks < 4:
+        return synth.english_like((nblocks - 1) * bl + tail, seed=40)
+    k = nblocks // 4
     return np.concatenate([synth.english_like(2 * k * bl, seed=41), synth.uniform_random(k * bl, seed=42),
-                           synth.dna_like((nblocks - 3 * k) * bl + tail, seed=43, block=bl)])
+                           synth.dna_like((nblocks - 3 * k - 1) * bl + tail, seed=43, block=bl)])
 
 
 def test_c_multi_entry_on_all_visible_gpus(orc):
