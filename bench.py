@@ -46,6 +46,21 @@ WORKLOADS = {
 
 
 def make_input(kind, size, seed, block_len):
+    """Seeded synthetic input.  SALZ_BENCH_CACHE=<dir> keeps generated inputs as .npy files
+    (A/B scripts that run bench.py many times in one box visit; never set by the driver)."""
+    cache = os.environ.get("SALZ_BENCH_CACHE")
+    if cache:
+        path = os.path.join(cache, "%s_%d_%d_%d.npy" % (kind, size, seed, block_len))
+        if os.path.exists(path):
+            return np.load(path)
+        data = _make_input(kind, size, seed, block_len)
+        os.makedirs(cache, exist_ok=True)
+        np.save(path, data)
+        return data
+    return _make_input(kind, size, seed, block_len)
+
+
+def _make_input(kind, size, seed, block_len):
     from salz_b200 import synth
     if kind == "english":
         return synth.english_like(size, seed=seed)

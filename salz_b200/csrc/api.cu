@@ -99,6 +99,9 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     Workspace &ws = c->ws;
     memset(&ws, 0, sizeof(ws));
     ws.parseSegments = ps ? atoi(ps) : 0;
+    const char *scm = getenv("SALZ_SCATTER"), *sgr = getenv("SALZ_SORT_GROUP");
+    ws.scatterMode = scm ? atoi(scm) : 2;
+    ws.sortGroup = sgr ? atoi(sgr) : 4;
     cudaDeviceGetAttribute(&ws.numSMs, cudaDevAttrMultiProcessorCount, device);
     if (ws.numSMs <= 0) ws.numSMs = 148;
     int logS = 12;
@@ -133,6 +136,7 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
          dalloc(c, &ws.symBits, B) && dalloc(c, &ws.h0, B);
     ok = ok && dalloc(c, &ws.hist, B * 8 * 256) && dalloc(c, &ws.digitBase, B * 8 * 256);
     ok = ok && dalloc(c, &ws.tileState, (ws.tileCap + 1) * 256);
+    ok = ok && dalloc(c, &ws.sched, ws.tileCap * 8) && dalloc(c, &ws.passDone, B * 8);
     ok = ok && dalloc(c, &ws.aggHead, ws.tileCap) && dalloc(c, &ws.aggPst, ws.tileCap) && dalloc(c, &ws.aggKeep, ws.tileCap);
     ok = ok && dalloc(c, &ws.counters, 16);
     ok = ok && dalloc(c, &ws.plcp, M) && dalloc(c, &ws.lcp, M) && dalloc(c, &ws.tileMax, M / 1024 + 1);

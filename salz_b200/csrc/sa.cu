@@ -556,6 +556,333 @@ k_scatter(const uint64_t *__restrict__ keysIn, const uint32_t *__restrict__ vals
     }
 }
 
+// ---- the radix scatter pass, TMA-staged (packed elements) --------------------------------
+// Same pass as k_scatter, restructured around Blackwell's bulk-async copy engine:
+//
+//  * tiles arrive in a two-slot shared-memory ring by cp.async.bulk (1-D TMA) completing on an
+//    mbarrier: thread 0 issues the copy of tile i+1 at the top of tile i, so the next tile's
+//    keys are in flight in shared memory instead of in 24 registers per thread; the slot a
+//    tile arrived in is reused as its digit-ordered staging area once the keys are in registers
+//  * ranking handles two keys per step with two peer-mask arrays: the shared-memory round
+//    trips of a step (two atomicOr, then six independent loads) overlap, where the one-key
+//    form chains four dependent round trips per key (ncu: 41 % of the stall samples of
+//    k_scatter were short-scoreboard waits inside that chain, profiles/r02_v0_*)
+//  * one launch can run SEVERAL passes (PassPlan.sched): tickets are ordered block-group-major
+//    - all passes over a group of a few blocks, then the next group - so that what pass k
+//    writes (8 MB per block) is still in the 126 MB L2 when pass k+1 reads it.  A tile of
+//    pass k+1 may start once all tiles of its block have finished pass k (passDone counters,
+//    released with a gpu-scope fence, acquired by the thread that issues the TMA load,
+//    followed by a proxy fence since the data is read through the async proxy).  Tickets are
+//    handed out in schedule order, so everything a CTA waits for is running or finished.
+//
+// Look-back states carry the pass in their flag bits (tag = pass + 1): one state array
+// serves all passes of a launch without being cleared in between.
+struct PassPlan {
+    const uint32_t *sched;   // [numTickets] tile | pass << 26; null: ticket t = tile t of pass `pass0`
+    uint32_t numTickets;
+    int pass0;               // first pass of this launch (index into digitBase)
+    int shift0;              // bit position of this launch's first digit
+    uint32_t *passDone;      // [B][MAXP] tiles that have finished (block, pass); null without sched
+};
+
+constexpr uint32_t ST_TAG_SHIFT = 26, ST_VAL_MASK = (1u << 26) - 1;   // flag:2 | tag:4 | value:26
+constexpr size_t SCATTER_TMA_SMEM = 2 * (size_t)TILE * 8 + 3 * (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 256;
+#ifndef SALZ_TCTAS
+#define SALZ_TCTAS 2
+#endif
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// bulk-async copy global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <int RANK2>
+__global__ void __launch_bounds__(TT, SALZ_TCTAS)
+k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const uint32_t *__restrict__ digitBase,
+              uint32_t *tileState)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t *slot0 = (uint64_t *)smem;                  // [2][TILE] arriving tile, then its keys in digit order
+    uint32_t *wcnt = (uint32_t *)(slot0 + 2 * TILE);     // [WARPS][256] per-warp digit counts -> running offsets
+    uint32_t *maskA = wcnt + WARPS * 256;                // [WARPS][256] peer masks (self-cleaning)
+    uint32_t *maskB = maskA + WARPS * 256;               // [WARPS][256] second key of a pair
+    uint32_t *dstart = maskB + WARPS * 256;              // [256]
+    uint32_t *gbase = dstart + 256;                      // [256]
+    uint32_t *scratch = gbase + 256;                     // [16]
+    uint32_t *sdesc = scratch + 16;                      // [2][8] ticket, tile, pass, b, lt, first, valid, pending
+    uint64_t *mbar = (uint64_t *)(sdesc + 16);           // [2]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t *state = tileState + 256;
+    uint32_t *mycnt = wcnt + warp * 256;
+    uint32_t *myA = maskA + warp * 256, *myB = maskB + warp * 256;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t laneBit = 1u << lane;
+
+    // thread 0: start the copy of the tile described in sdesc[k] into slot k
+    auto issue = [&](int k) {
+        const uint32_t *sd = sdesc + 8 * k;
+        const uint64_t *src = ((sd[2] & 1) ? buf1 : buf0) + sd[5];
+        const uint32_t bytes = ((sd[6] + 1u) & ~1u) * 8u;        // whole 16-byte units (the list is padded)
+        mbar_expect_tx(&mbar[k], bytes);
+        tma_load_1d(slot0 + (size_t)k * TILE, src, bytes, &mbar[k]);
+    };
+    // a tile of pass ps > 0 may be read once its block has finished pass ps - 1
+    auto ready = [&](const uint32_t *sd) -> bool {
+        if (sd[2] == 0) return true;
+        const uint32_t need = lv.tileBase[sd[3] + 1] - lv.tileBase[sd[3]];
+        if (ld_acquire(pp.passDone + (size_t)sd[3] * MAXP + (sd[2] - 1)) < need) return false;
+        asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes of other SMs -> async-proxy read
+        return true;
+    };
+    // thread 0: claim a ticket and describe its tile in sdesc[k]; the copy starts right away
+    // unless the block's previous pass is still running - then it is left pending (sd[7]) and
+    // issued when the tile becomes the current one (never wait here: the tile that is missing
+    // may be this CTA's own current tile)
+    auto fetch = [&](int k) {
+        const uint32_t t = atomicAdd(tileState, 1u);
+        uint32_t *sd = sdesc + 8 * k;
+        sd[0] = t;
+        sd[7] = 0;
+        if (t >= pp.numTickets) return;
+        uint32_t tile = t, ps = 0;
+        if (pp.sched) {
+            const uint32_t e = pp.sched[t];
+            tile = e & ST_VAL_MASK;
+            ps = e >> ST_TAG_SHIFT;
+        }
+        const uint4 d = lv.tileDesc[tile];
+        sd[1] = tile; sd[2] = ps; sd[3] = d.x; sd[4] = d.y; sd[5] = d.z; sd[6] = d.w;
+        if (ready(sd)) issue(k);
+        else sd[7] = 1;
+    };
+
+    for (int i = tid; i < 3 * WARPS * 256; i += TT) wcnt[i] = 0;   // counts and both mask arrays
+    if (tid == 0) {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        fetch(0);
+    }
+    __syncthreads();
+
+    for (uint32_t it = 0;; it++) {
+        const int k = it & 1;
+        const uint32_t *sd = sdesc + 8 * k;
+        if (sd[0] >= pp.numTickets) break;
+        const uint32_t tile = sd[1], ps = sd[2];
+        TileLoc tl;
+        tl.b = sd[3]; tl.lt = sd[4]; tl.first = sd[5]; tl.valid = sd[6];
+        const int shift = pp.shift0 + 8 * (int)ps;
+        const uint32_t tag = (ps + 1) << ST_TAG_SHIFT;
+        uint64_t *skeys = slot0 + (size_t)k * TILE;
+        uint64_t *keysOut = (ps & 1) ? buf0 : buf1;
+        if (tid == 0) {
+            if (sd[7]) {              // pending: everything with a smaller ticket is running or done
+                while (!ready(sd)) __nanosleep(64);
+                issue(k);
+            }
+            fetch(k ^ 1);             // slot k^1: everybody left it at the previous tile's last barrier
+        }
+
+        mbar_wait(&mbar[k], (it >> 1) & 1);
+        uint64_t key[ITEMS];
+        uint32_t dd[ITEMS / 2];       // digits of a pair of keys, 8 bits each
+        uint32_t uni = 0;             // bit j: both digits of pair j are warp-uniform
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
+            key[i] = (idx < tl.valid) ? skeys[idx] : ~0ull;
+        }
+        // early counts: published before the ranking so that successors find aggregates
+#pragma unroll
+        for (int j = 0; j < ITEMS / 2; j++) {
+            const uint32_t d0 = (uint32_t)(key[2 * j] >> shift) & 255u, d1 = (uint32_t)(key[2 * j + 1] >> shift) & 255u;
+            const uint32_t p2 = d0 | (d1 << 8);
+            dd[j] = p2;
+            if (__reduce_and_sync(0xffffffffu, p2) == __reduce_or_sync(0xffffffffu, p2)) {
+                uni |= 1u << j;
+                if (lane == 0) {   // one lane adds for the warp: 32 same-address atomics would serialise
+                    atomicAdd(&mycnt[d0], 32u);
+                    atomicAdd(&mycnt[d1], 32u);
+                }
+            } else {
+                atomicAdd(&mycnt[d0], 1u);
+                atomicAdd(&mycnt[d1], 1u);
+            }
+        }
+        __syncthreads();   // counts complete; every key of the slot is in registers
+
+        uint32_t total = 0, ex = 0;
+        if (tid < 256) {
+            uint32_t sum = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) {
+                const uint32_t c = wcnt[w * 256 + tid];
+                wcnt[w * 256 + tid] = sum;
+                sum += c;
+            }
+            total = sum;
+            const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
+            st_relaxed(&state[(size_t)tile * 256 + tid], (tl.lt == 0 ? LB_INCL : LB_AGG) | tag | cnt);
+            // exclusive scan over the 256 digits: warp scan, then the eight warp totals
+            uint32_t inc = total;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (lane == 31) scratch[warp] = inc;
+            ex = inc - total;
+        }
+        __syncthreads();
+        if (tid < 256) {
+            uint32_t wb = 0;
+#pragma unroll
+            for (int w = 0; w < 7; w++) wb += (w < warp) ? scratch[w] : 0u;
+            ex += wb;
+            dstart[tid] = ex;
+        }
+        __syncthreads();
+
+        // ranking, two keys per step: peers of a lane = lanes of the warp holding the same digit
+#pragma unroll
+        for (int j = 0; j < ITEMS / 2; j++) {
+            const uint32_t d0 = dd[j] & 255u, d1 = dd[j] >> 8;
+            uint32_t r0, r1;
+            if ((uni >> j) & 1u) {
+                const uint32_t c0 = mycnt[d0];
+                const uint32_t c1 = mycnt[d1];
+                r0 = c0 + lane;
+                r1 = ((d0 == d1) ? c0 + 32 : c1) + lane;
+                __syncwarp();
+                if (lane == 0) {
+                    if (d0 == d1) mycnt[d0] = c0 + 64;
+                    else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
+                }
+            } else if (RANK2) {
+                atomicOr(&myA[d0], laneBit);
+                atomicOr(&myB[d1], laneBit);
+                __syncwarp();
+                const uint32_t m0 = myA[d0], m1 = myB[d1];
+                const uint32_t x = myA[d1];     // first keys with my second key's digit
+                const uint32_t y = myB[d0];     // second keys with my first key's digit
+                const uint32_t c0 = mycnt[d0], c1 = mycnt[d1];
+                __syncwarp();
+                r0 = c0 + __popc(m0 & lt_mask);
+                r1 = c1 + __popc(x) + __popc(m1 & lt_mask);
+                if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0) + __popc(y); }
+                if (lane == __ffs(m1) - 1) { myB[d1] = 0; if (x == 0) mycnt[d1] = c1 + __popc(m1); }
+            } else {
+                atomicOr(&myA[d0], laneBit);
+                __syncwarp();
+                const uint32_t m0 = myA[d0];
+                const uint32_t c0 = mycnt[d0];
+                __syncwarp();
+                r0 = c0 + __popc(m0 & lt_mask);
+                if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0); }
+                __syncwarp();
+                atomicOr(&myA[d1], laneBit);
+                __syncwarp();
+                const uint32_t m1 = myA[d1];
+                const uint32_t c1 = mycnt[d1];
+                __syncwarp();
+                r1 = c1 + __popc(m1 & lt_mask);
+                if (lane == __ffs(m1) - 1) { myA[d1] = 0; mycnt[d1] = c1 + __popc(m1); }
+            }
+            skeys[dstart[d0] + r0] = key[2 * j];
+            skeys[dstart[d1] + r1] = key[2 * j + 1];
+            __syncwarp();   // leaders' stores before the next step's atomics
+        }
+        // the warp's counters are its own again: cleared for the next tile
+        for (int i = lane; i < 256; i += 32) mycnt[i] = 0;
+
+        if (tid < 256) {
+            uint32_t prev = 0;
+            if (tl.lt != 0) {
+                uint32_t t = tile - 1;
+                for (bool done = false; !done;) {
+                    const uint32_t w = min((uint32_t)LBW, tl.lt - (tile - 1 - t));  // stay inside the block
+                    uint32_t sv[LBW];
+#pragma unroll
+                    for (int q = 0; q < LBW; q++)
+                        sv[q] = ((uint32_t)q < w) ? ld_relaxed(&state[(size_t)(t - q) * 256 + tid]) : 0u;
+#pragma unroll
+                    for (int q = 0; q < LBW; q++) {
+                        if (done || (uint32_t)q >= w) break;
+                        if ((sv[q] & (15u << ST_TAG_SHIFT)) != tag) break;   // not published for this pass yet
+                        prev += sv[q] & ST_VAL_MASK;
+                        t--;
+                        if ((sv[q] >> 30) == 2) done = true;
+                    }
+                }
+                const uint32_t cnt = total - ((tid == 255) ? (TILE - tl.valid) : 0u);
+                st_relaxed(&state[(size_t)tile * 256 + tid], LB_INCL | tag | (prev + cnt));
+            }
+            gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pp.pass0 + ps) * 256 + tid] + prev - ex;
+        }
+        __syncthreads();
+
+        for (uint32_t j = tid; j < tl.valid; j += TT) {
+            const uint64_t kk = skeys[j];
+            keysOut[gbase[(uint32_t)(kk >> shift) & 255u] + j] = kk;
+        }
+        // this thread's generic-proxy accesses to the slot precede the bulk copy that refills it
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();   // the slot is free, the tile is written
+        if (tid == 0 && pp.passDone) {
+            __threadfence();
+            atomicAdd(&pp.passDone[(size_t)tl.b * MAXP + ps], 1u);
+        }
+    }
+}
+
+// Schedule of a multi-pass launch: group-major (all passes over `group` consecutive blocks,
+// then the next group), inside a group pass-major, inside a pass in tile order (look-back
+// predecessors first).  One thread per (pass, tile).
+__global__ void __launch_bounds__(256) k_sched(const uint32_t *__restrict__ tileBase, const uint4 *__restrict__ tileDesc,
+                                               uint32_t numTiles, int passes, int group, uint32_t *__restrict__ sched)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= numTiles * (uint32_t)passes) return;
+    const uint32_t tile = i % numTiles, ps = i / numTiles;
+    const uint32_t b = tileDesc[tile].x;
+    const uint32_t g0 = b - b % (uint32_t)group;                 // first block of the group
+    const uint32_t gEnd = min(g0 + (uint32_t)group, tileDesc[numTiles - 1].x + 1);
+    const uint32_t gTile0 = tileBase[g0], gTiles = tileBase[gEnd] - gTile0;
+    sched[(size_t)gTile0 * passes + (size_t)ps * gTiles + (tile - gTile0)] = tile | (ps << ST_TAG_SHIFT);
+}
+
 // ---- re-rank + compaction -------------------------------------------------------------
 // Element k of a block's segment starts a new group ("head") when its key field
 // differs from its predecessor's, or when it is the first of the segment.  From
@@ -1284,24 +1611,59 @@ template <bool PACKED>
 int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, int shift0, int src, int dst)
 {
     Workspace &ws = s.ws;
-    const size_t smem = PACKED ? SCATTER_SMEM_PACKED : SCATTER_SMEM_PAIRS;
-    const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SCATTER_MIN_CTAS));
     if (s.msSort) CK(cudaEventRecord(s.evA, s.st));
-    for (int ps = 0; ps < passes; ps++) {
+    if (PACKED && ws.scatterMode > 0) {
+        // TMA-staged kernel.  sortGroup > 0: all passes in ONE launch, tickets block-group-major
+        // (a group's lists stay in L2 from pass to pass); otherwise a launch per pass.
+        const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SALZ_TCTAS));
+        const bool fused = ws.sortGroup > 0 && passes > 1;
         CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
-        if (s.matchAny)
-            k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst], ws.vals[dst & 1],
-                                                              view(ws, v), tiles, shift0 + 8 * ps, ps, ws.digitBase,
-                                                              ws.tileState);
-        else
-            k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst],
-                                                               ws.vals[dst & 1], view(ws, v), tiles, shift0 + 8 * ps, ps,
-                                                               ws.digitBase, ws.tileState);
-        s.lc.launches += 1;
-        s.lc.sort_launches += 1;
-        s.lc.sort_elems += count;
-        s.lc.sort_bytes += (uint64_t)count * (PACKED ? 16 : 24);
-        std::swap(src, dst);
+        if (fused) {
+            const uint32_t tickets = tiles * (uint32_t)passes;
+            CK(cudaMemsetAsync(ws.passDone, 0, (size_t)s.bd.B * MAXP * 4, s.st));
+            k_sched<<<(tickets + 255) / 256, 256, 0, s.st>>>(ws.tileBase[v], ws.tileDesc[v], tiles, passes, ws.sortGroup, ws.sched);
+            const PassPlan pp = {ws.sched, tickets, 0, shift0, ws.passDone};
+            if (ws.scatterMode == 2)
+                k_scatter_tma<1><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+            else
+                k_scatter_tma<0><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+            s.lc.launches += 2;
+            s.lc.sort_launches += 1;
+            if (passes & 1) std::swap(src, dst);
+        } else {
+            for (int ps = 0; ps < passes; ps++) {
+                if (ps) CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
+                const PassPlan pp = {nullptr, tiles, ps, shift0 + 8 * ps, nullptr};
+                if (ws.scatterMode == 2)
+                    k_scatter_tma<1><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                else
+                    k_scatter_tma<0><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                s.lc.launches += 1;
+                s.lc.sort_launches += 1;
+                std::swap(src, dst);
+            }
+        }
+        s.lc.sort_elems += (uint64_t)count * passes;
+        s.lc.sort_bytes += (uint64_t)count * 16 * passes;
+    } else {
+        const size_t smem = PACKED ? SCATTER_SMEM_PACKED : SCATTER_SMEM_PAIRS;
+        const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SCATTER_MIN_CTAS));
+        for (int ps = 0; ps < passes; ps++) {
+            CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
+            if (s.matchAny)
+                k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst], ws.vals[dst & 1],
+                                                                  view(ws, v), tiles, shift0 + 8 * ps, ps, ws.digitBase,
+                                                                  ws.tileState);
+            else
+                k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst],
+                                                                   ws.vals[dst & 1], view(ws, v), tiles, shift0 + 8 * ps, ps,
+                                                                   ws.digitBase, ws.tileState);
+            s.lc.launches += 1;
+            s.lc.sort_launches += 1;
+            s.lc.sort_elems += count;
+            s.lc.sort_bytes += (uint64_t)count * (PACKED ? 16 : 24);
+            std::swap(src, dst);
+        }
     }
     if (s.msSort) CK(cudaEventRecord(s.evB, s.st));
     CK(cudaGetLastError());
@@ -1514,6 +1876,8 @@ int sa_init_device()
     CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
     CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
     CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+    CK(cudaFuncSetAttribute(k_scatter_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
+    CK(cudaFuncSetAttribute(k_scatter_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     return 0;
 }
 

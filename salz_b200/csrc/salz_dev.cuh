@@ -52,6 +52,10 @@ struct Workspace {
     uint32_t *hist;      // [Bmax][8][256] digit histograms for the coming sort
     uint32_t *digitBase; // [Bmax][8][256] exclusive scans of hist
     uint32_t *tileState; // [1 + tileCap][256]: ticket, then look-back states
+    uint32_t *sched;     // [8 * tileCap] ticket order of a multi-pass scatter launch (tile | pass << 26)
+    uint32_t *passDone;  // [Bmax][8] tiles that have finished (block, pass) in that launch
+    int scatterMode;     // 0 = register-staged k_scatter, 1 = TMA-staged, 2 = TMA-staged + two keys per ranking step
+    int sortGroup;       // > 0: all passes of a sort in one launch, block groups of this many blocks (L2-resident)
     // rerank scans
     uint32_t *aggHead;  // [tileCap]
     uint32_t *aggPst;   // [tileCap]
