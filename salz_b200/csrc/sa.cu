@@ -586,10 +586,15 @@ struct PassPlan {
 };
 
 constexpr uint32_t ST_TAG_SHIFT = 26, ST_VAL_MASK = (1u << 26) - 1;   // flag:2 | tag:4 | value:26
-constexpr size_t SCATTER_TMA_SMEM = 2 * (size_t)TILE * 8 + 3 * (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 256;
 #ifndef SALZ_TCTAS
 #define SALZ_TCTAS 2
 #endif
+#ifndef SALZ_TSLOTS
+#define SALZ_TSLOTS 2
+#endif
+constexpr int TSLOTS = SALZ_TSLOTS;                    // shared-memory slots of the tile ring
+constexpr int TTHREADS = TT + 32;                      // consumer warps + the producer warp
+constexpr size_t SCATTER_TMA_SMEM = (size_t)TSLOTS * TILE * 8 + 3 * (size_t)WARPS * 256 * 4 + 2 * 256 * 4 + 512;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
@@ -599,6 +604,10 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
@@ -625,79 +634,84 @@ __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+// barrier among the consumer warps only (the producer warp never joins it)
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(TT) : "memory"); }
 
 template <int RANK2>
-__global__ void __launch_bounds__(TT, SALZ_TCTAS)
+__global__ void __launch_bounds__(TTHREADS, SALZ_TCTAS)
 k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const uint32_t *__restrict__ digitBase,
               uint32_t *tileState)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t *slot0 = (uint64_t *)smem;                  // [2][TILE] arriving tile, then its keys in digit order
-    uint32_t *wcnt = (uint32_t *)(slot0 + 2 * TILE);     // [WARPS][256] per-warp digit counts -> running offsets
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint64_t *slot0 = (uint64_t *)smem;                  // [TSLOTS][TILE] arriving tile, then its keys in digit order
+    uint32_t *wcnt = (uint32_t *)(slot0 + TSLOTS * TILE);   // [WARPS][256] per-warp digit counts -> running offsets
     uint32_t *maskA = wcnt + WARPS * 256;                // [WARPS][256] peer masks (self-cleaning)
     uint32_t *maskB = maskA + WARPS * 256;               // [WARPS][256] second key of a pair
     uint32_t *dstart = maskB + WARPS * 256;              // [256]
     uint32_t *gbase = dstart + 256;                      // [256]
     uint32_t *scratch = gbase + 256;                     // [16]
-    uint32_t *sdesc = scratch + 16;                      // [2][8] ticket, tile, pass, b, lt, first, valid, pending
-    uint64_t *mbar = (uint64_t *)(sdesc + 16);           // [2]
+    uint32_t *sdesc = scratch + 16;                      // [TSLOTS][8] ticket, tile, pass, b, lt, first, valid
+    uint64_t *full = (uint64_t *)(sdesc + 8 * 4);        // [TSLOTS] tile (and its descriptor) has arrived
+    uint64_t *empty = full + 4;                          // [TSLOTS] consumers have left the slot
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint32_t *state = tileState + 256;
+
+    if (tid == 0) {
+        for (int k = 0; k < TSLOTS; k++) {
+            mbar_init(&full[k], 1);
+            mbar_init(&empty[k], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = tid; i < 3 * WARPS * 256; i += TTHREADS) wcnt[i] = 0;   // counts and both mask arrays
+    __syncthreads();
+
+    if (warp == WARPS) {
+        // ---- producer warp (one lane): tickets, tile descriptors, dependencies, bulk copies ----
+        if (lane != 0) return;
+        for (uint32_t it = 0;; it++) {
+            const int k = it % TSLOTS;
+            if (it >= (uint32_t)TSLOTS) mbar_wait(&empty[k], ((it / TSLOTS) - 1) & 1);
+            const uint32_t t = atomicAdd(tileState, 1u);
+            uint32_t *sd = sdesc + 8 * k;
+            sd[0] = t;
+            if (t >= pp.numTickets) {
+                mbar_arrive(&full[k]);   // wakes the consumers, who read the ticket and leave
+                return;
+            }
+            uint32_t tile = t, ps = 0;
+            if (pp.sched) {
+                const uint32_t e = pp.sched[t];
+                tile = e & ST_VAL_MASK;
+                ps = e >> ST_TAG_SHIFT;
+            }
+            const uint4 d = lv.tileDesc[tile];
+            sd[1] = tile; sd[2] = ps; sd[3] = d.x; sd[4] = d.y; sd[5] = d.z; sd[6] = d.w;
+            if (ps > 0) {
+                // the block's previous pass must be complete; its tiles have smaller tickets, so
+                // they are running or done (the consumer warps of this CTA keep working meanwhile)
+                const uint32_t need = lv.tileBase[d.x + 1] - lv.tileBase[d.x];
+                const uint32_t *flag = pp.passDone + (size_t)d.x * MAXP + (ps - 1);
+                while (ld_acquire(flag) < need) __nanosleep(100);
+                asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes of other SMs -> async-proxy read
+            }
+            const uint64_t *src = ((ps & 1) ? buf1 : buf0) + d.z;
+            const uint32_t bytes = ((d.w + 1u) & ~1u) * 8u;        // whole 16-byte units (the list is padded)
+            mbar_expect_tx(&full[k], bytes);
+            tma_load_1d(slot0 + (size_t)k * TILE, src, bytes, &full[k]);
+        }
+    }
+
+    // ---- consumer warps ----
     uint32_t *mycnt = wcnt + warp * 256;
     uint32_t *myA = maskA + warp * 256, *myB = maskB + warp * 256;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t laneBit = 1u << lane;
 
-    // thread 0: start the copy of the tile described in sdesc[k] into slot k
-    auto issue = [&](int k) {
-        const uint32_t *sd = sdesc + 8 * k;
-        const uint64_t *src = ((sd[2] & 1) ? buf1 : buf0) + sd[5];
-        const uint32_t bytes = ((sd[6] + 1u) & ~1u) * 8u;        // whole 16-byte units (the list is padded)
-        mbar_expect_tx(&mbar[k], bytes);
-        tma_load_1d(slot0 + (size_t)k * TILE, src, bytes, &mbar[k]);
-    };
-    // a tile of pass ps > 0 may be read once its block has finished pass ps - 1
-    auto ready = [&](const uint32_t *sd) -> bool {
-        if (sd[2] == 0) return true;
-        const uint32_t need = lv.tileBase[sd[3] + 1] - lv.tileBase[sd[3]];
-        if (ld_acquire(pp.passDone + (size_t)sd[3] * MAXP + (sd[2] - 1)) < need) return false;
-        asm volatile("fence.proxy.async;" ::: "memory");   // generic-proxy writes of other SMs -> async-proxy read
-        return true;
-    };
-    // thread 0: claim a ticket and describe its tile in sdesc[k]; the copy starts right away
-    // unless the block's previous pass is still running - then it is left pending (sd[7]) and
-    // issued when the tile becomes the current one (never wait here: the tile that is missing
-    // may be this CTA's own current tile)
-    auto fetch = [&](int k) {
-        const uint32_t t = atomicAdd(tileState, 1u);
-        uint32_t *sd = sdesc + 8 * k;
-        sd[0] = t;
-        sd[7] = 0;
-        if (t >= pp.numTickets) return;
-        uint32_t tile = t, ps = 0;
-        if (pp.sched) {
-            const uint32_t e = pp.sched[t];
-            tile = e & ST_VAL_MASK;
-            ps = e >> ST_TAG_SHIFT;
-        }
-        const uint4 d = lv.tileDesc[tile];
-        sd[1] = tile; sd[2] = ps; sd[3] = d.x; sd[4] = d.y; sd[5] = d.z; sd[6] = d.w;
-        if (ready(sd)) issue(k);
-        else sd[7] = 1;
-    };
-
-    for (int i = tid; i < 3 * WARPS * 256; i += TT) wcnt[i] = 0;   // counts and both mask arrays
-    if (tid == 0) {
-        mbar_init(&mbar[0], 1);
-        mbar_init(&mbar[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        fetch(0);
-    }
-    __syncthreads();
-
     for (uint32_t it = 0;; it++) {
-        const int k = it & 1;
+        const int k = it % TSLOTS;
+        mbar_wait(&full[k], (it / TSLOTS) & 1);
         const uint32_t *sd = sdesc + 8 * k;
         if (sd[0] >= pp.numTickets) break;
         const uint32_t tile = sd[1], ps = sd[2];
@@ -707,15 +721,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         const uint32_t tag = (ps + 1) << ST_TAG_SHIFT;
         uint64_t *skeys = slot0 + (size_t)k * TILE;
         uint64_t *keysOut = (ps & 1) ? buf0 : buf1;
-        if (tid == 0) {
-            if (sd[7]) {              // pending: everything with a smaller ticket is running or done
-                while (!ready(sd)) __nanosleep(64);
-                issue(k);
-            }
-            fetch(k ^ 1);             // slot k^1: everybody left it at the previous tile's last barrier
-        }
 
-        mbar_wait(&mbar[k], (it >> 1) & 1);
         uint64_t key[ITEMS];
         uint32_t dd[ITEMS / 2];       // digits of a pair of keys, 8 bits each
         uint32_t uni = 0;             // bit j: both digits of pair j are warp-uniform
@@ -741,7 +747,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                 atomicAdd(&mycnt[d1], 1u);
             }
         }
-        __syncthreads();   // counts complete; every key of the slot is in registers
+        consumer_sync();   // counts complete; every key of the slot is in registers
 
         uint32_t total = 0, ex = 0;
         if (tid < 256) {
@@ -765,7 +771,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             if (lane == 31) scratch[warp] = inc;
             ex = inc - total;
         }
-        __syncthreads();
+        consumer_sync();
         if (tid < 256) {
             uint32_t wb = 0;
 #pragma unroll
@@ -773,9 +779,9 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             ex += wb;
             dstart[tid] = ex;
         }
-        __syncthreads();
+        consumer_sync();
 
-        // ranking, two keys per step: peers of a lane = lanes of the warp holding the same digit
+        // ranking: peers of a lane = lanes of the warp holding the same digit
 #pragma unroll
         for (int j = 0; j < ITEMS / 2; j++) {
             const uint32_t d0 = dd[j] & 255u, d1 = dd[j] >> 8;
@@ -790,7 +796,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                     if (d0 == d1) mycnt[d0] = c0 + 64;
                     else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
                 }
-            } else if (RANK2) {
+            } else if (RANK2) {   // two keys per step, two mask arrays: the round trips of a step overlap
                 atomicOr(&myA[d0], laneBit);
                 atomicOr(&myB[d1], laneBit);
                 __syncwarp();
@@ -851,7 +857,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             }
             gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pp.pass0 + ps) * 256 + tid] + prev - ex;
         }
-        __syncthreads();
+        consumer_sync();
 
         for (uint32_t j = tid; j < tl.valid; j += TT) {
             const uint64_t kk = skeys[j];
@@ -859,10 +865,13 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
         // this thread's generic-proxy accesses to the slot precede the bulk copy that refills it
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncthreads();   // the slot is free, the tile is written
-        if (tid == 0 && pp.passDone) {
-            __threadfence();
-            atomicAdd(&pp.passDone[(size_t)tl.b * MAXP + ps], 1u);
+        consumer_sync();   // the slot is free, the tile is written
+        if (tid == 0) {
+            mbar_arrive(&empty[k]);
+            if (pp.passDone) {
+                __threadfence();
+                atomicAdd(&pp.passDone[(size_t)tl.b * MAXP + ps], 1u);
+            }
         }
     }
 }
@@ -1624,9 +1633,9 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
             k_sched<<<(tickets + 255) / 256, 256, 0, s.st>>>(ws.tileBase[v], ws.tileDesc[v], tiles, passes, ws.sortGroup, ws.sched);
             const PassPlan pp = {ws.sched, tickets, 0, shift0, ws.passDone};
             if (ws.scatterMode == 2)
-                k_scatter_tma<1><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
             else
-                k_scatter_tma<0><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
             s.lc.launches += 2;
             s.lc.sort_launches += 1;
             if (passes & 1) std::swap(src, dst);
@@ -1635,9 +1644,9 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
                 if (ps) CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
                 const PassPlan pp = {nullptr, tiles, ps, shift0 + 8 * ps, nullptr};
                 if (ws.scatterMode == 2)
-                    k_scatter_tma<1><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                    k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
                 else
-                    k_scatter_tma<0><<<grid, TT, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                    k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
                 s.lc.launches += 1;
                 s.lc.sort_launches += 1;
                 std::swap(src, dst);
