@@ -3,6 +3,7 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
                     [--workload english256|dna1g|single512|random512|mixed] [--level L] [--mib M]
+                    [--no-extras]
 
 A "step" is one pass of the whole hot path (suffix array -> PLCP/LCP -> PSV/NSV
 + match lengths -> optimal parse -> bit/byte emission) over the workload's
@@ -12,19 +13,25 @@ synthetic English-like text cut into 1 MiB blocks (CLI level 5), per GPU.
   value  compress MB/s (input bytes), input and output resident in HBM
   e2e    same through the host-buffer C-ABI call (H2D + kernels + D2H timed)
   roofline / cpu_baseline: see DESIGN.md "Measurement"
+  verified  sampled records of the TIMED output equal the compiled reference's bytes,
+            and the device-resident and host-buffer arms produced the same stream;
+            without that no value is printed
+  extra.workloads  the other BASELINE configs (N = 1: configs[2], [4], level 9) and, at every
+            N, configs[3]: the 8 GiB mixed stream STRONG-sharded over the N ranks, with a
+            digest of the assembled stream that must not depend on N
+  extra.cli  wall seconds of `programs/salz -k -f -5` beside the reference CLI (N = 1)
 
-N > 1 (torchrun): every rank compresses its own shard of the stream (weak
-scaling, no data-path collective) and the per-block encoded sizes are
-all-gathered over NCCL inside the timed step.
+N > 1 (torchrun): every rank compresses its own shard (weak scaling, no data-path
+collective); the per-block encoded sizes are all-gathered over NCCL by the C library
+(salz_cuda_comm_allgather_sizes, csrc/multi_gpu.cu) inside the timed step.
 """
 import argparse
-import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 import numpy as np
@@ -34,6 +41,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "compress_MBps_input"
 UNIT = "MB/s"
+MIXED_TOTAL_MIB = 8192
 
 WORKLOADS = {
     # name: (generator, MiB per GPU, description)
@@ -43,6 +51,13 @@ WORKLOADS = {
     "random512": ("random", 512, "512 MiB + 4096 B uniform random bytes (configs[4]b)"),
     "mixed": ("mixed", 1024, "1 GiB + 4096 B per GPU of the 8 GiB mixed stream (configs[3])"),
 }
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
 
 
 def make_input(kind, size, seed, block_len):
@@ -71,15 +86,17 @@ def _make_input(kind, size, seed, block_len):
     if kind == "random":
         return synth.uniform_random(size, seed=seed + 3)
     if kind == "mixed":
-        return synth.mixed_stream(size, seed=seed + 2)
+        return synth.mixed_stream(size, seed=seed + 2, workers=max(1, host_cores() - 1))
     raise ValueError(kind)
 
 
-def host_cores():
-    try:
-        return len(os.sched_getaffinity(0))
-    except AttributeError:
-        return os.cpu_count() or 1
+def make_config(args, desc, block_len, nblocks, size, batch, world):
+    """The `config` object: identical in the b200 and the reference arm."""
+    return {"workload": desc, "level": args.level, "block_len": block_len, "blocks_per_gpu": nblocks,
+            "bytes_per_gpu": size, "batch_blocks": batch, "seed": args.seed,
+            "l2": "inputs and workspace larger than L2 (%.0f MiB text, ~%.0f GiB workspace per pass)"
+                  % (size / 2**20, 96.0 * size / 2**30),
+            "parallelism": "blocks sharded over %d GPU(s); NCCL all-gather of sizes" % world}
 
 
 class ClockSampler:
@@ -102,6 +119,7 @@ class ClockSampler:
                  "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
+        return self
 
     def stop(self):
         if self.proc is None:
@@ -132,16 +150,21 @@ class ClockSampler:
                 "samples": len(sm), "power_w_max": max(power)}
 
 
-def run_cpu_reference(data, block_len, nblocks_sample, threads):
-    """The reference's own encoder (oracle/_ref, compiled in place from the upstream
-    sources) or, when that prebuilt library is absent, the oracle restatement, on
-    `nblocks_sample` blocks with `threads` host threads.  Returns (seconds, bytes, kind)."""
+# ---- the reference on the host cores (checker / baseline only) -------------------------------------
+
+def reference_oracle():
+    """oracle/_ref/libsalz_ref.so: the unmodified upstream sources compiled by oracle/Makefile."""
+    from oracle.binding import Ref
+    if not Ref.available():
+        raise SystemExit("bench.py: oracle/_ref/libsalz_ref.so (the compiled reference) is absent; "
+                         "build it where /root/reference exists (make -C oracle)")
+    return Ref()
+
+
+def run_cpu_reference(orc, data, block_len, nblocks_sample, threads):
+    """`nblocks_sample` blocks through the reference's salz_encode_safe, one block per call,
+    `threads` host threads.  Returns (seconds, bytes)."""
     from concurrent.futures import ThreadPoolExecutor
-    from oracle.binding import Port, Ref
-    if Ref.available():
-        orc, kind = Ref(), "reference"
-    else:
-        orc, kind = Port(), "port"
     nblocks = (len(data) + block_len - 1) // block_len
     nb = min(nblocks, nblocks_sample)
     blocks = [data[b * block_len: (b + 1) * block_len] for b in range(nb)]
@@ -153,19 +176,14 @@ def run_cpu_reference(data, block_len, nblocks_sample, threads):
     else:
         with ThreadPoolExecutor(threads) as ex:  # ctypes releases the GIL during the call
             list(ex.map(orc.encode, blocks))
-    return time.perf_counter() - t0, nbytes, kind
+    return time.perf_counter() - t0, nbytes
 
 
-def run_cpu_libsais(data, block_len, nblocks_sample, threads):
+def run_cpu_libsais(ref, data, block_len, nblocks_sample, threads):
     """SA only, beside the device SA stage (CPU baseline iii): upstream
-    `libsais()` from oracle/_ref on the same blocks -- one thread, one block per thread
-    on all host cores, and `libsais_omp(threads)` block after block.  GB/s of text, or
-    None without the compiled reference."""
+    `libsais()` on the same blocks -- one thread, one block per thread on all host cores,
+    and `libsais_omp(threads)` block after block.  GB/s of text."""
     from concurrent.futures import ThreadPoolExecutor
-    from oracle.binding import Ref
-    if not Ref.available():
-        return None
-    ref = Ref()
     nblocks = (len(data) + block_len - 1) // block_len
     blocks = [data[b * block_len: (b + 1) * block_len] for b in range(min(nblocks, nblocks_sample))]
     blocks = [b[: len(b) - 8] for b in blocks if len(b) > 8]   # the reference sorts T[0..N-8)
@@ -187,38 +205,329 @@ def run_cpu_libsais(data, block_len, nblocks_sample, threads):
     return out
 
 
+def config0_reference_cli():
+    """BASELINE configs[0]: the reference CLI, as shipped (one thread), on 16 MiB + 4096 B of
+    order-2 Markov text: compress, decompress, cmp (ref scripts/bench.sh:44-62)."""
+    from salz_b200 import synth
+    cli = os.path.join(ROOT, "oracle", "_ref", "salz_ref")
+    if not os.path.exists(cli):
+        return None
+    data = synth.markov_text_lanes((16 << 20) + 4096, seed=42)
+    d = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        src = os.path.join(d, "markov16.bin")
+        data.tofile(src)
+        out = {"input": "16 MiB + 4096 B order-2 Markov text (27 symbols, Dirichlet 0.15, seed 42), tmpfs",
+               "cli": "oracle/_ref/salz_ref (unmodified reference, 1 thread)"}
+        for lvl in (5, 9):
+            t0 = time.perf_counter()
+            subprocess.run([cli, "-k", "-f", "-q", "-%d" % lvl, src], check=True)
+            tc = time.perf_counter() - t0
+            os.rename(src, src + ".orig")
+            t0 = time.perf_counter()
+            subprocess.run([cli, "-d", "-k", "-f", "-q", src + ".salz"], check=True)
+            td = time.perf_counter() - t0
+            same = open(src, "rb").read() == open(src + ".orig", "rb").read()
+            out["level%d" % lvl] = {"compress_s": tc, "decompress_s": td, "roundtrip_ok": same,
+                                    "compress_MBps": len(data) / tc / 1e6,
+                                    "ratio": len(data) / os.path.getsize(src + ".salz")}
+            os.unlink(src)
+            os.rename(src + ".orig", src)
+        return out
+    finally:
+        subprocess.run(["rm", "-rf", d])
+
+
+def cli_walltime(data, level):
+    """Wall seconds of this repository's `salz -k -f -<level>` beside the reference CLI on the
+    same file (tmpfs, page-cache warm); outputs must be identical."""
+    ours = os.path.join(ROOT, "programs", "salz")
+    ref = os.path.join(ROOT, "oracle", "_ref", "salz_ref")
+    if not (os.path.exists(ours) and os.path.exists(ref)):
+        return None
+    d = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        a = os.path.join(d, "a.bin")
+        b = os.path.join(d, "b.bin")
+        data.tofile(a)
+        data.tofile(b)
+        res = {"file_bytes": int(len(data)), "level": level, "where": "tmpfs, page cache warm"}
+        times = []
+        for _ in range(2):   # the first run pays CUDA context creation with a cold driver
+            t0 = time.perf_counter()
+            p = subprocess.run([ours, "-k", "-f", "-%d" % level, a], capture_output=True, text=True)
+            times.append(time.perf_counter() - t0)
+            if p.returncode != 0:
+                res["error"] = p.stderr[-300:]
+                return res
+            res["log_line"] = p.stderr.strip().splitlines()[-1] if p.stderr.strip() else ""
+        res["salz_b200_wall_s"] = min(times)
+        res["salz_b200_wall_s_first"] = times[0]
+        t0 = time.perf_counter()
+        p = subprocess.run([ref, "-k", "-f", "-%d" % level, b], capture_output=True, text=True)
+        res["reference_wall_s"] = time.perf_counter() - t0
+        res["reference_log_line"] = p.stderr.strip().splitlines()[-1] if p.stderr.strip() else ""
+        res["identical_output"] = open(a + ".salz", "rb").read() == open(b + ".salz", "rb").read()
+        res["speedup_wall"] = res["reference_wall_s"] / res["salz_b200_wall_s"]
+        return res
+    finally:
+        subprocess.run(["rm", "-rf", d])
+
+
 def reference_arm(args, kind, mib, block_len, desc):
-    """bench.py --impl reference: the reference CPU implementation on the host cores."""
+    """bench.py --impl reference: the reference CPU implementation on the host cores, every
+    block of the workload per step (the same config object as the b200 arm)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    orc = reference_oracle()
     cores = host_cores()
-    sample_blocks = max(cores, min(128, max(1, (64 << 20) // block_len)))
-    size = min(mib << 20, sample_blocks * block_len) + 4096
+    size = (mib << 20) + 4096
     data = make_input(kind, size, args.seed, block_len)
     nb = (len(data) + block_len - 1) // block_len
-    for _ in range(args.warmup):
-        run_cpu_reference(data, block_len, min(nb, cores), cores)
+    batch = min(args.batch_blocks or nb, (1 << 30) // block_len)
+    for _ in range(min(args.warmup, 1)):
+        run_cpu_reference(orc, data, block_len, min(nb, 2 * cores), cores)
     tot_s, tot_b = 0.0, 0
-    k = "reference"
     for _ in range(args.steps):
-        s, b, k = run_cpu_reference(data, block_len, nb, cores)
+        s, b = run_cpu_reference(orc, data, block_len, nb, cores)
         tot_s += s
         tot_b += b
     v = tot_b / tot_s / 1e6
-    sample = "%d blocks of %d B (%s) per step, %d threads, one block per reference call" % (
+    sample = "all %d blocks of %d B (%s) per step, %d threads, one block per reference call" % (
         nb, block_len, kind, cores)
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/i32", "data": "synthetic",
-        "config": {"workload": desc, "level": args.level, "block_len": block_len},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": k, "sample": sample},
+        "config": make_config(args, desc, block_len, nb, size, batch, args.gpus),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
     return 0
+
+
+# ---- the GPU arm ----------------------------------------------------------------------------------
+
+class Env:
+    """torch / torch.distributed plumbing of one rank."""
+
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            torch.cuda.set_device(self.local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+            self.dist = dist
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+        self.dev = torch.device("cuda", self.local_rank)
+        torch.cuda.set_device(self.dev)
+        self.stream = torch.cuda.Stream(device=self.dev)
+        # the C library's own NCCL communicator for the size all-gather: rank 0 makes the id,
+        # torch.distributed only ships its 128 bytes
+        import salz_b200
+        from salz_b200 import api
+        uid = [api.unique_id() if self.rank == 0 else None]
+        if self.dist is not None:
+            self.dist.broadcast_object_list(uid, src=0)
+        self.comm = salz_b200.ShardComm(self.local_rank, uid[0], self.rank, self.world)
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def timed(self, fn, steps):
+        torch = self.torch
+        ev0 = torch.cuda.Event(enable_timing=True)
+        ev1 = torch.cuda.Event(enable_timing=True)
+        self.barrier()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(self.stream):
+            ev0.record(self.stream)
+        for _ in range(steps):
+            fn()
+        with torch.cuda.stream(self.stream):
+            ev1.record(self.stream)
+        self.barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms = ev0.elapsed_time(ev1)
+        t = torch.tensor([ms, wall], dtype=torch.float64, device=self.dev)
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1])
+
+    def close(self):
+        self.comm.close()
+        if self.dist is not None:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def split_records(sizes):
+    """[(offset, length)] of every record payload in a framed stream, and the stream length."""
+    offs = np.concatenate([[0], np.cumsum(sizes.astype(np.int64) + 4)])
+    return [(int(offs[b]) + 4, int(sizes[b])) for b in range(len(sizes))], int(offs[-1])
+
+
+def verify_stream(orc, data, block_len, stream, sizes, nsample=8):
+    """Sampled records (first, last, the largest = PLAIN if any, the smallest, evenly spread
+    others) of a framed stream against the compiled reference.  Returns (ok, blocks checked)."""
+    recs, total = split_records(sizes)
+    if total != len(stream):
+        return False, []
+    nb = len(sizes)
+    picks = {0, nb - 1, int(np.argmax(sizes)), int(np.argmin(sizes))}
+    picks |= {int(x) for x in np.linspace(0, nb - 1, num=min(nb, nsample)).astype(int)}
+    ok = True
+    for b in sorted(picks):
+        off, ln = recs[b]
+        want = orc.encode(data[b * block_len: (b + 1) * block_len])
+        hdr = int.from_bytes(bytes(stream[off - 4: off]), "little")
+        if hdr != ln or bytes(stream[off: off + ln]) != want:
+            ok = False
+    return ok, sorted(picks)
+
+
+def run_workload(env, orc, data, block_len, steps, warmup, batch, all_sizes_total=None, do_e2e=True, clocks=False):
+    """One workload on this rank: device-resident arm, host-buffer arm, verification.
+    `all_sizes_total` = blocks of the whole (strong-sharded) stream for the all-gather; None =
+    every rank contributes a shard of equal block count (weak scaling)."""
+    import salz_b200
+    torch = env.torch
+    size = len(data)
+    nblocks = (size + block_len - 1) // block_len
+    batch = min(batch or nblocks, (1 << 30) // block_len, 65535)
+    enc = salz_b200.SalzCuda(device=env.local_rank, max_block_len=block_len, max_batch_blocks=batch)
+    enc.set_stream(env.stream.cuda_stream)
+    res = {"blocks": nblocks, "bytes": size, "batch_blocks": batch}
+    try:
+        h_src = torch.from_numpy(data).pin_memory()
+        cap = salz_b200.api.stream_len_max(size, block_len)
+        h_dst = torch.empty(cap, dtype=torch.uint8).pin_memory()
+        d_src = h_src.to(env.dev)
+        d_dst = torch.empty(cap, dtype=torch.uint8, device=env.dev)
+        sizes = np.zeros(nblocks, np.uint32)
+        out_len = [0]
+        gathered = [None]
+        ntotal = all_sizes_total if all_sizes_total is not None else nblocks * env.world
+
+        def gather():
+            # the only exchange of the path: per-block encoded sizes -> record offsets (SURVEY 8e)
+            gathered[0] = env.comm.allgather_sizes(sizes, ntotal)
+
+        def step_device():
+            with torch.cuda.stream(env.stream):
+                out_len[0] = enc.encode_stream_ptr(d_src.data_ptr(), size, block_len, d_dst.data_ptr(), cap, sizes,
+                                                   device=True)
+            gather()
+
+        def step_host():
+            with torch.cuda.stream(env.stream):
+                out_len[0] = enc.encode_stream_ptr(h_src.data_ptr(), size, block_len, h_dst.data_ptr(), cap, sizes,
+                                                   device=False)
+            gather()
+
+        for _ in range(warmup):
+            step_device()
+        enc.reset_stats()
+        sampler = ClockSampler(env.local_rank).start() if clocks and env.rank == 0 else None
+        ms_dev, wall_dev = env.timed(step_device, steps)
+        res["clocks"] = sampler.stop() if sampler else None
+        res["stats"] = enc.stats()
+        res["ms_dev"], res["wall_dev"] = ms_dev, wall_dev
+        res["out_bytes"] = int(out_len[0])
+        dev_sizes = sizes.copy()
+        dev_stream = d_dst[: out_len[0]].cpu().numpy()
+        if do_e2e:
+            step_host()
+            ms_e2e, _ = env.timed(step_host, steps)
+            res["ms_e2e"] = ms_e2e
+            host_stream = h_dst[: out_len[0]].numpy()
+            res["same_stream_both_arms"] = bool(np.array_equal(dev_sizes, sizes) and len(host_stream) == len(dev_stream)
+                                                and np.array_equal(host_stream, dev_stream))
+        ok, picks = verify_stream(orc, data, block_len, dev_stream, dev_sizes)
+        res["verified"] = bool(ok and res.get("same_stream_both_arms", True))
+        res["verified_blocks"] = picks
+        res["sizes"] = dev_sizes
+        res["stream"] = dev_stream
+        res["all_sizes"], res["offsets"] = gathered[0]
+        res["gathers"] = env.comm.gathers()
+    finally:
+        enc.close()
+    return res
+
+
+def summarize(res, steps, world_bytes):
+    """Compact record of a workload for extra.workloads."""
+    st = res["stats"]
+    out = {"value": world_bytes * steps / (res["ms_dev"] * 1e-3) / 1e6, "unit": UNIT,
+           "ms_per_step": res["ms_dev"] / steps, "verified": res["verified"],
+           "doubling_rounds_per_step": st["doubling_rounds"] / steps, "ratio": res["bytes"] / max(1, res["out_bytes"]),
+           "blocks_per_gpu": res["blocks"], "batch_blocks": res["batch_blocks"],
+           "stage_ms_per_step": {k: st[k] / steps for k in
+                                 ("ms_sa", "ms_sort", "ms_lcp", "ms_ansv", "ms_parse", "ms_emit", "ms_total")},
+           "clocks": res.get("clocks")}
+    if "ms_e2e" in res:
+        out["e2e"] = {"value": world_bytes * steps / (res["ms_e2e"] * 1e-3) / 1e6, "unit": UNIT,
+                      "ms_per_step": res["ms_e2e"] / steps}
+    return out
+
+
+def mixed_strong(env, orc, args):
+    """configs[3]: the 8 GiB + 4096 B mixed stream, level 5, strong-sharded over the ranks:
+    rank r encodes block range salz_cuda_block_range(8193, r, N); sizes all-gathered by the C
+    library; the digest of the assembled stream (sha256 over the per-record sha256s in stream
+    order) must be the same at every N."""
+    from salz_b200 import api, synth
+    block_len = 1 << 20
+    total = (args.mixed_mib << 20) + 4096
+    nblocks = (total + block_len - 1) // block_len
+    lo, hi = api.block_range(nblocks, env.rank, env.world)
+    t0 = time.perf_counter()
+    data = synth.mixed_stream(total, seed=args.seed + 2, lo=lo * block_len, hi=min(total, hi * block_len),
+                              workers=max(1, host_cores() // env.world))
+    gen_s = time.perf_counter() - t0
+    res = run_workload(env, orc, data, block_len, 2, 1, 1024, all_sizes_total=nblocks, clocks=True)
+    # per-record digests, gathered in block order
+    recs, _ = split_records(res["sizes"])
+    mine = np.zeros((hi - lo, 32), np.uint8)
+    for i, (off, ln) in enumerate(recs):
+        mine[i] = np.frombuffer(hashlib.sha256(res["stream"][off - 4: off + ln].tobytes()).digest(), np.uint8)
+    torch = env.torch
+    per = (nblocks + env.world - 1) // env.world
+    buf = torch.zeros((per, 32), dtype=torch.uint8, device=env.dev)
+    buf[: hi - lo] = torch.from_numpy(mine).to(env.dev)
+    flags = torch.tensor([1.0 if res["verified"] else 0.0], device=env.dev)
+    if env.dist is not None:
+        out = [torch.empty_like(buf) for _ in range(env.world)]
+        env.dist.all_gather(out, buf)
+        env.dist.all_reduce(flags, op=env.dist.ReduceOp.MIN)
+    else:
+        out = [buf]
+    if env.rank != 0:
+        return None
+    h = hashlib.sha256()
+    for r in range(env.world):
+        l, hh = api.block_range(nblocks, r, env.world)
+        h.update(out[r][: hh - l].cpu().numpy().tobytes())
+    s = summarize(res, 2, total)
+    s.update({"workload": "%d MiB + 4096 B mixed stream (configs[3]), level 5, %d blocks strong-sharded over %d GPU(s)"
+                          % (args.mixed_mib, nblocks, env.world),
+              "scaling": "strong", "stream_bytes": int(res["offsets"][-1]),
+              "stream_sha256_of_record_sha256s": h.hexdigest(),
+              "verified": bool(flags.item() > 0.5), "sizes_allgathered_blocks": int(len(res["all_sizes"])),
+              "host_generation_s": gen_s})
+    return s
 
 
 def main():
@@ -234,6 +543,8 @@ def main():
     ap.add_argument("--batch-blocks", type=int, default=0, help="blocks per device batch (0 = all)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip extra.workloads / extra.cli")
+    ap.add_argument("--mixed-mib", type=int, default=MIXED_TOTAL_MIB, help="size of the configs[3] stream")
     args = ap.parse_args()
     kind, mib, desc = WORKLOADS[args.workload]
     if args.mib:
@@ -244,111 +555,62 @@ def main():
     if args.impl == "reference":
         return reference_arm(args, kind, mib, block_len, desc)
 
-    import torch
-    import salz_b200
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
-    dev = torch.device("cuda", local_rank)
-    torch.cuda.set_device(dev)
+    env = Env()
+    orc = reference_oracle()   # checker of the timed output + cpu_baseline leg
+    rank, world = env.rank, env.world
+    torch = env.torch
 
     size = (mib << 20) + 4096
     data = make_input(kind, size, args.seed + rank, block_len)
     nblocks = (size + block_len - 1) // block_len
-    batch = args.batch_blocks or nblocks
-    batch = min(batch, (1 << 30) // block_len)
-    enc = salz_b200.SalzCuda(device=local_rank, max_block_len=block_len, max_batch_blocks=batch)
-    stream = torch.cuda.Stream(device=dev)
-    enc.set_stream(stream.cuda_stream)
+    batch = min(args.batch_blocks or nblocks, (1 << 30) // block_len)
 
-    h_src = torch.from_numpy(data).pin_memory()
-    cap = salz_b200.api.stream_len_max(size, block_len)
-    h_dst = torch.empty(cap, dtype=torch.uint8).pin_memory()
-    d_src = h_src.to(dev)
-    d_dst = torch.empty(cap, dtype=torch.uint8, device=dev)
-    sizes = np.zeros(nblocks, np.uint32)
-    d_sizes = torch.zeros(nblocks, dtype=torch.int32, device=dev)
-    gathered = torch.zeros(world * nblocks, dtype=torch.int32, device=dev) if world > 1 else None
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    out_len = [0]
-
-    def step_device():
-        with torch.cuda.stream(stream):
-            out_len[0] = enc.encode_stream_ptr(d_src.data_ptr(), size, block_len, d_dst.data_ptr(), cap, sizes,
-                                               device=True)
-            if dist is not None:
-                # the only exchange of the path: per-block encoded sizes -> stream offsets
-                d_sizes.copy_(torch.from_numpy(sizes.astype(np.int32)), non_blocking=True)
-                dist.all_gather_into_tensor(gathered, d_sizes)
-
-    def step_host():
-        with torch.cuda.stream(stream):
-            out_len[0] = enc.encode_stream_ptr(h_src.data_ptr(), size, block_len, h_dst.data_ptr(), cap, sizes,
-                                               device=False)
-            if dist is not None:
-                d_sizes.copy_(torch.from_numpy(sizes.astype(np.int32)), non_blocking=True)
-                dist.all_gather_into_tensor(gathered, d_sizes)
-                gathered.cpu()
-
-    def timed(fn, steps):
-        ev0 = torch.cuda.Event(enable_timing=True)
-        ev1 = torch.cuda.Event(enable_timing=True)
-        barrier()
-        t0 = time.perf_counter()
-        with torch.cuda.stream(stream):
-            ev0.record(stream)
-        for _ in range(steps):
-            fn()
-        with torch.cuda.stream(stream):
-            ev1.record(stream)
-        barrier()
-        wall = (time.perf_counter() - t0) * 1e3
-        ms = ev0.elapsed_time(ev1)
-        t = torch.tensor([ms, wall], dtype=torch.float64, device=dev)
-        if dist is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t[0]), float(t[1])
-
-    # ---- device-resident arm ---------------------------------------------------
-    for _ in range(args.warmup):
-        step_device()
-    enc.reset_stats()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-    ms_dev, wall_dev = timed(step_device, args.steps)
-    clocks = sampler.stop() if rank == 0 else None
-    st = enc.stats()
-    out_bytes = out_len[0]
-
-    # ---- end-to-end arm (host buffers through the C ABI) ---------------------------
+    res = run_workload(env, orc, data, block_len, args.steps, args.warmup, batch, do_e2e=not args.no_e2e, clocks=True)
+    st = res["stats"]
+    ms_dev, wall_dev = res["ms_dev"], res["wall_dev"]
+    clocks = res["clocks"]
+    out_bytes = res["out_bytes"]
+    ok = torch.tensor([1.0 if res["verified"] else 0.0], device=env.dev)
+    if env.dist is not None:
+        env.dist.all_reduce(ok, op=env.dist.ReduceOp.MIN)
+    verified = bool(ok.item() > 0.5)
     e2e = None
     if not args.no_e2e:
-        step_host()
-        ms_e2e, wall_e2e = timed(step_host, args.steps)
-        e2e = {"value": world * size * args.steps / (ms_e2e * 1e-3) / 1e6, "unit": UNIT,
-               "h2d_bytes_per_step": size, "d2h_bytes_per_step": int(out_len[0]),
-               "ms_per_step": ms_e2e / args.steps}
+        e2e = {"value": world * size * args.steps / (res["ms_e2e"] * 1e-3) / 1e6, "unit": UNIT,
+               "h2d_bytes_per_step": size, "d2h_bytes_per_step": int(out_bytes),
+               "ms_per_step": res["ms_e2e"] / args.steps}
+    gathers = res["gathers"]
+    res.pop("stream")
+
+    # ---- the other configs --------------------------------------------------------------------
+    workloads = {}
+    cli = None
+    if not args.no_extras and args.workload == "english256" and not args.mib and args.level == 5:
+        if world == 1:
+            for name, lvl, bb in (("dna1g", 5, 512), ("single512", 5, 512), ("random512", 5, 512), ("english256", 9, 0)):
+                k2, m2, d2 = WORKLOADS[name]
+                bl2 = 1 << (15 + lvl)
+                dat = data if name == "english256" else make_input(k2, (m2 << 20) + 4096, args.seed, bl2)
+                r2 = run_workload(env, orc, dat, bl2, 2, 1, bb, clocks=True)
+                r2.pop("stream")
+                s2 = summarize(r2, 2, len(dat))
+                s2["workload"] = d2 + ", level %d" % lvl
+                workloads[name + ("_level9" if lvl == 9 else "")] = s2
+                verified = verified and s2["verified"]
+                del dat
+            cli = cli_walltime(data, 5)
+        m = mixed_strong(env, orc, args)
+        if m is not None:
+            workloads["mixed8g_strong"] = m
+            verified = verified and m["verified"]
 
     if rank != 0:
-        if dist is not None:
-            dist.barrier()
-            dist.destroy_process_group()
+        env.close()
         return 0
+    if not verified:
+        print("bench.py: the timed output does NOT equal the reference's bytes; no value reported", file=sys.stderr)
+        env.close()
+        return 1
 
     peaks = {}
     try:
@@ -359,33 +621,37 @@ def main():
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
 
     # Per-kernel rooflines, algorithmic bytes over CUDA-event time on the library's
-    # stream.  The dominant kernel (largest share of the step) is reported as "roofline"; since the
-    # serial-chain parse took that place from the radix pass, the sort pass follows in "roofline_others".
+    # stream.  The kernel with the largest share of the step is reported as "roofline".
     traffic = {}
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_v15_traffic.json")))
-    except (OSError, ValueError):
-        pass
+    for name in ("r02_traffic.json", "r01_v15_traffic.json"):
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", name)))
+            break
+        except (OSError, ValueError):
+            pass
 
-    def tr(name):
-        t = traffic.get(name)
-        return t["dram_bytes_per_launch"] if t else None
+    def tr(*names):
+        for n in names:
+            t = traffic.get(n)
+            if t:
+                return t["dram_bytes_per_launch"]
+        return None
 
     positions = float(st["input_bytes"]) - 8.0 * st["blocks"]
     sort_bytes = float(st["sort_bytes"])
     sort_launches = max(1, st["sort_launches"])
     parse_launches = max(1, args.steps * ((nblocks + batch - 1) // batch))
+    ptr = [tr("k_parse_warm"), tr("k_parse"), tr("k_choose")]
     cands = [
         {"kernel": "k_parse", "bound": "hbm", "alg_bytes": 32.0 * positions, "ms": st["ms_parse"],
-         "launches": parse_launches, "traffic": (tr("k_parse_warm") + tr("k_parse") + tr("k_choose"))
-         if tr("k_parse_warm") and tr("k_parse") and tr("k_choose") else None,
+         "launches": parse_launches, "traffic": sum(ptr) if all(ptr) else None,
          "note": "whole parse stage per batch (k_parse: shortened first pass + full pass, k_choose incl. the jump "
                  "pointers; its CUDA-event time): serial (min,+) chains, 4 per consumer warp, 16 per SM, "
                  "latency-bound by construction; 32 B/position = candidates 16 + cost 4 + choice 8 + jump 4; "
                  "traffic = sum over the stage's launches"},
-        {"kernel": "k_scatter", "bound": "hbm", "alg_bytes": sort_bytes, "ms": st["ms_sort"],
-         "launches": sort_launches, "traffic": tr("k_scatter<1, 0>"),
-         "note": "one LSD radix pass: 16 B per list element (read + write of a packed element)"},
+        {"kernel": "k_scatter_tma", "bound": "hbm", "alg_bytes": sort_bytes, "ms": st["ms_sort"],
+         "launches": sort_launches, "traffic": tr("k_scatter_tma<0>", "k_scatter_tma<1>", "k_scatter<1, 0>"),
+         "note": "LSD radix scatter, TMA-staged: 16 B per list element per pass (read + write of a packed element)"},
     ]
     rl = []
     for c in cands:
@@ -405,14 +671,16 @@ def main():
     if not args.no_cpu_baseline:
         cores = host_cores()
         nb = min(nblocks, max(cores, min(128, (128 << 20) // block_len)))
-        s, b, k = run_cpu_reference(data, block_len, nb, cores)
-        cpu = {"value": b / s / 1e6, "unit": UNIT, "cores": cores, "kind": k,
+        s, b = run_cpu_reference(orc, data, block_len, nb, cores)
+        cpu = {"value": b / s / 1e6, "unit": UNIT, "cores": cores, "kind": "reference",
                "sample": "first %d of %d blocks (%d B each), %d threads, one block per reference call, %.1f s wall"
                          % (nb, nblocks, block_len, cores, s)}
         nb1 = min(nblocks, 4)
-        s1, b1, _ = run_cpu_reference(data, block_len, nb1, 1)
+        s1, b1 = run_cpu_reference(orc, data, block_len, nb1, 1)
         cpu["single_thread_value"] = b1 / s1 / 1e6
-        cpu["sa"] = run_cpu_libsais(data, block_len, nb, cores)
+        cpu["sa"] = run_cpu_libsais(orc, data, block_len, nb, cores)
+        if not args.no_extras and world == 1:
+            cpu["config0_reference_cli"] = config0_reference_cli()
 
     n_in = st["input_bytes"]
     value = world * size * args.steps / (ms_dev * 1e-3) / 1e6
@@ -420,12 +688,8 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8/i32", "data": "synthetic",
-        "config": {"workload": desc, "level": args.level, "block_len": block_len, "blocks_per_gpu": nblocks,
-                   "bytes_per_gpu": size, "batch_blocks": batch, "seed": args.seed,
-                   "l2": "inputs and workspace larger than L2 (%.0f MiB text, ~%.0f GiB workspace per pass)"
-                         % (size / 2**20, 96.0 * size / 2**30),
-                   "parallelism": "blocks sharded over %d GPU(s); NCCL all-gather of sizes" % world},
-        "e2e": e2e, "gpu_launches": int(st["launches"]), "clocks": clocks,
+        "config": make_config(args, desc, block_len, nblocks, size, batch, world),
+        "e2e": e2e, "gpu_launches": int(st["launches"]), "clocks": clocks, "verified": verified,
         "roofline": roofline, "roofline_others": roofline_others, "cpu_baseline": cpu,
         "extra": {
             "compressed_bytes_per_gpu": int(out_bytes), "ratio": size / max(1, out_bytes),
@@ -434,12 +698,13 @@ def main():
             "doubling_rounds_per_step": st["doubling_rounds"] / args.steps,
             "stage_ms_per_step": {k: st[k] / args.steps for k in
                                   ("ms_sa", "ms_sort", "ms_lcp", "ms_ansv", "ms_parse", "ms_emit", "ms_total")},
+            "verified_blocks": res["verified_blocks"],
+            "nccl_size_allgathers": int(gathers),
+            "workloads": workloads, "cli": cli,
         },
     }
     print(json.dumps(line))
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    env.close()
     return 0
 
 
