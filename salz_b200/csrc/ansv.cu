@@ -73,13 +73,16 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     }
     int2 *cd = cand2 + 2 * gb;
     int4 *cd4 = (int4 *)cd;
+    // candidates leave as 8- and 16-byte pieces of 32-byte sectors, in text order: they are
+    // kept in L2 (evict_last) until the other pieces arrive; SA and LCP stream through
+    const uint64_t keep = l2_evict_last(), stream = l2_evict_first();
 
     for (int j = tid; j < ATS; j += AT) {
         const uint32_t r = t0 + j;
         const int k = (j >> 5) * APAD + (j & 31);
         if (r < n) {
-            sv[k] = SA[gb + r] << 8;
-            sm[k] = LCP[gb + r];
+            sv[k] = ld_stream(SA + gb + r, stream) << 8;
+            sm[k] = ld_stream(LCP + gb + r, stream);
         }
     }
     __syncthreads();
@@ -98,11 +101,11 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
                 const uint32_t lk = sv[sb + top] & 0xffu;
                 const int32_t tm = sm[sb + top];   // min LCP over (PSV of top, top]
                 if (lk & LINK_PM) {                // its PSV lies outside the segment: NSV half only
-                    cd[2 * topVal + 1] = make_int2(topVal - v, acc);
+                    st_hint(&cd[2 * topVal + 1], make_int2(topVal - v, acc), keep);
                     top = -1;
                 } else {                           // both known: one 16-byte store instead of two 8-byte ones
                     const int32_t pv = (int32_t)(sv[sb + (int)lk] >> 8);
-                    cd4[topVal] = make_int4(topVal - pv, tm, topVal - v, acc);
+                    st_hint(&cd4[topVal], make_int4(topVal - pv, tm, topVal - v, acc), keep);
                     top = (int)lk;
                     topVal = pv;
                 }
@@ -182,9 +185,9 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
                 acc = min(acc, sm[e]);
                 e = s * APAD + (int)(sv[e] & 0x7fu);
             }
-            cd[2 * v] = make_int2(v - (int32_t)(sv[e] >> 8), acc);
+            st_hint(&cd[2 * v], make_int2(v - (int32_t)(sv[e] >> 8), acc), keep);
         } else if (firstTile) {
-            cd[2 * v] = make_int2(v + 1, 0);       // no PSV: offs = p - (-1), len 0 (ref lib/salz.c:546-560)
+            st_hint(&cd[2 * v], make_int2(v + 1, 0), keep);       // no PSV: offs = p - (-1), len 0 (ref lib/salz.c:546-560)
         } else {
             farItems[atomicAdd(farCount, 1u)] = far_item((uint32_t)gb + t0 + tid * AL + i, 0, acc);
         }
@@ -215,13 +218,13 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
                 int f = s * APAD;                  // first prefix minimum of that segment
                 while ((int32_t)(sv[f] >> 8) > v) f = s * APAD + (int)(sv[f] & 0x7fu);
                 const int2 ns = make_int2(v - (int32_t)(sv[f] >> 8), min(acc, sm[f]));
-                if (havePsv) cd4[v] = make_int4(ps.x, ps.y, ns.x, ns.y);
-                else cd[2 * v + 1] = ns;
+                if (havePsv) st_hint(&cd4[v], make_int4(ps.x, ps.y, ns.x, ns.y), keep);
+                else st_hint(&cd[2 * v + 1], ns, keep);
             } else if (lastTile) {
-                if (havePsv) cd4[v] = make_int4(ps.x, ps.y, v + 1, 0);
-                else cd[2 * v + 1] = make_int2(v + 1, 0);
+                if (havePsv) st_hint(&cd4[v], make_int4(ps.x, ps.y, v + 1, 0), keep);
+                else st_hint(&cd[2 * v + 1], make_int2(v + 1, 0), keep);
             } else {
-                if (havePsv) cd[2 * v] = ps;
+                if (havePsv) st_hint(&cd[2 * v], ps, keep);
                 farItems[atomicAdd(farCount, 1u)] = far_item((uint32_t)gb + t0 + tid * AL + e, 1, acc);
             }
             accR = min(accR, sm[sb + e]);

@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(LT) k_plcp_apply(const uint32_t *__restrict__ 
     if (p < n) {
         int32_t pl = v - (int32_t)p;
         V[g] = pl;
-        lcp[(g & ~Smask) | ((uint32_t)rank[g] & 0xffffffu)] = pl;
+        st_hint(&lcp[(g & ~Smask) | ((uint32_t)rank[g] & 0xffffffu)], pl, l2_evict_last());   // 4-byte scatter by rank: sectors complete in L2
     }
 }
 

@@ -1181,6 +1181,7 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
     HK agg;
     const HK exLoc = hk_block_excl(v, &agg, scratch);   // exclusive inside the tile
     const size_t gb = (size_t)tl.b << logS;
+    const uint64_t keep = l2_evict_last();   // rank / SA scatters: partial sectors wait in L2 for their neighbours
     // Round 0: the one pst of a segment is its first element, whatever the tile.
     const uint32_t pst0 = tl.first - tl.lt * TILE + 1;
     // Elements whose head (and pst) lie inside the tile do not need the prefix over the
@@ -1199,8 +1200,8 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
                     if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
                     else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
                     const uint32_t r = prim + (curHead - curPst);
-                    rank[gb + p] = rk_make(round, prim, r);
-                    if (head[i] && head[i + 1]) SA[gb + r] = p;
+                    st_hint(&rank[gb + p], rk_make(round, prim, r), keep);
+                    if (head[i] && head[i + 1]) st_hint(&SA[gb + r], p, keep);
                 }
             }
         }
@@ -1240,9 +1241,9 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
             if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
             else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
             const uint32_t r = prim + (curHead - curPst);  // SA slot of the group head
-            if (!done) rank[gb + p] = rk_make(round, prim, r);
+            if (!done) st_hint(&rank[gb + p], rk_make(round, prim, r), keep);
             if (head[i] && head[i + 1]) {
-                if (!done) SA[gb + r] = p;
+                if (!done) st_hint(&SA[gb + r], p, keep);
             } else {
                 if (PACKED) {
                     stage[outLoc] = ((uint64_t)r << (2 * logS)) | p;
@@ -1524,6 +1525,7 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     __syncthreads();   // everyone has read the sorted neighbours: sk can take the survivors
 
     uint32_t curHead = ex.head, curPst = ex.pst, outIdx = ex.keep;
+    const uint64_t keepPol = l2_evict_last();
 #pragma unroll
     for (int i = 0; i < LITEMS; i++) {
         const int j = j0 + i;
@@ -1534,9 +1536,9 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             const uint32_t p = (uint32_t)k[i] & Smask;
             const uint32_t grp = (uint32_t)(k[i] >> (2 * logS));
             const uint32_t r = grp + (curHead - curPst);
-            rank[gb + p] = rk_make(round, grp, r);
+            st_hint(&rank[gb + p], rk_make(round, grp, r), keepPol);
             if (hd && hn) {
-                SA[gb + r] = p;
+                st_hint(&SA[gb + r], p, keepPol);
             } else {
                 sk[outIdx] = ((uint64_t)r << (2 * logS)) | p;
                 outIdx++;

@@ -147,6 +147,82 @@ __device__ __forceinline__ int factor_cost_bits(uint32_t offs, uint32_t len)
     return factor_pre_bits(offs) + 8 + factor_post_bits(len);
 }
 
+// ---- L2 residency hints ------------------------------------------------------
+// Scatters by text position (candidates, ranks, SA slots) write a fraction of a 32-byte
+// sector at a time; the other fractions arrive later from other CTAs.  Stores carry an
+// evict_last policy so that the partially written sectors wait in the 126 MB L2 for their
+// neighbours instead of going to DRAM as read-modify-write pairs; the streaming inputs of
+// the same kernels are read evict_first.
+#ifndef SALZ_L2_HINTS
+#define SALZ_L2_HINTS 1
+#endif
+__device__ __forceinline__ uint64_t l2_evict_last()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t l2_evict_first()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void st_hint(int4 *a, int4 v, uint64_t pol)
+{
+#if SALZ_L2_HINTS
+    asm volatile("st.global.L2::cache_hint.v4.s32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol) : "memory");
+#else
+    *a = v;
+#endif
+}
+__device__ __forceinline__ void st_hint(int2 *a, int2 v, uint64_t pol)
+{
+#if SALZ_L2_HINTS
+    asm volatile("st.global.L2::cache_hint.v2.s32 [%0], {%1, %2}, %3;" ::"l"(a), "r"(v.x), "r"(v.y), "l"(pol) : "memory");
+#else
+    *a = v;
+#endif
+}
+__device__ __forceinline__ void st_hint(uint64_t *a, uint64_t v, uint64_t pol)
+{
+#if SALZ_L2_HINTS
+    asm volatile("st.global.L2::cache_hint.u64 [%0], %1, %2;" ::"l"(a), "l"(v), "l"(pol) : "memory");
+#else
+    *a = v;
+#endif
+}
+__device__ __forceinline__ void st_hint(uint32_t *a, uint32_t v, uint64_t pol)
+{
+#if SALZ_L2_HINTS
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
+#else
+    *a = v;
+#endif
+}
+__device__ __forceinline__ void st_hint(int32_t *a, int32_t v, uint64_t pol)
+{
+#if SALZ_L2_HINTS
+    asm volatile("st.global.L2::cache_hint.s32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
+#else
+    *a = v;
+#endif
+}
+__device__ __forceinline__ uint32_t ld_stream(const uint32_t *a, uint64_t pol)
+{
+#if SALZ_L2_HINTS
+    uint32_t v;
+    asm volatile("ld.global.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(a), "l"(pol));
+    return v;
+#else
+    return *a;
+#endif
+}
+__device__ __forceinline__ int32_t ld_stream(const int32_t *a, uint64_t pol)
+{
+    return (int32_t)ld_stream((const uint32_t *)a, pol);
+}
+
 // ---- host-side launchers (one per pipeline stage) --------------------------
 struct LaunchCounter { uint64_t launches, sort_launches, sort_elems, sort_bytes; };
 
