@@ -375,6 +375,7 @@ int ansv_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounte
     k_ansv_far<<<148 * 8, 256, 0, st>>>(py, ws.blkN, farItems, farCount, (int2 *)ws.cand, ws.tilePreV, ws.tileSufV);
     k_cand0<<<(bd.B + 127) / 128, 128, 0, st>>>(ws.cand, bd.logS, bd.B);
     lc.launches += 4;
+    lc.alg_bytes += (uint64_t)bd.M * 24;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "salz_cuda: ansv_build: %s\n", cudaGetErrorString(e));

@@ -137,7 +137,6 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ok = ok && dalloc(c, &ws.hist, B * 8 * 256) && dalloc(c, &ws.digitBase, B * 8 * 256);
     ok = ok && dalloc(c, &ws.tileState, (ws.tileCap + 1) * 256);
     ok = ok && dalloc(c, &ws.sched, ws.tileCap * 8) && dalloc(c, &ws.passDone, B * 8);
-    ok = ok && dalloc(c, &ws.aggHead, ws.tileCap) && dalloc(c, &ws.aggPst, ws.tileCap) && dalloc(c, &ws.aggKeep, ws.tileCap);
     ok = ok && dalloc(c, &ws.counters, 16);
     ok = ok && dalloc(c, &ws.plcp, M) && dalloc(c, &ws.lcp, M) && dalloc(c, &ws.tileMax, M / 1024 + 1);
     for (int l = 1; l < 6 && ok; l++) {
@@ -247,7 +246,7 @@ static int run_batch(salz_cuda_ctx *c, int B, size_t Tstride, int framing, int u
     bd.maxN = maxN;
     CKC(c, cudaMemcpyAsync(ws.blkN, c->h_blkN, (size_t)B * 4, cudaMemcpyHostToDevice, st));
 
-    LaunchCounter lc = {0, 0, 0, 0};
+    LaunchCounter lc = {0, 0, 0, 0, 0};
     uint64_t algSa = 0;
     int rounds = 0;
     float msSort = 0.f;
@@ -281,11 +280,12 @@ static int run_batch(salz_cuda_ctx *c, int B, size_t Tstride, int framing, int u
     s.doubling_rounds += rounds;
     s.alg_bytes_sa += algSa;
     if (upto >= 5) {
-        s.alg_bytes_rest += (uint64_t)M * 99;
+        s.alg_bytes_rest += lc.alg_bytes;   // counted at the launch sites (salz_dev.cuh)
         s.blocks += B;
         for (int b = 0; b < B; b++) {
             s.input_bytes += c->h_blkN[b];
             s.output_bytes += c->h_outLen[b];
+            s.alg_bytes_rest += c->h_outLen[b];
         }
     }
     return 0;

@@ -173,60 +173,13 @@ __global__ void k_out_offsets(const uint32_t *__restrict__ blkOutLen, int B, int
     }
 }
 
-#ifndef SALZ_EMIT_WARP
-#define SALZ_EMIT_WARP 1
-#endif
-#if !SALZ_EMIT_WARP
-// One thread per chunk: assign token indices and bit offsets, write the
-// direct bytes, record which token owns the first bit of every word.
-__global__ void __launch_bounds__(128) k_emit_tokens(
-    const uint8_t *__restrict__ T, size_t Tstride, const uint32_t *__restrict__ blkN,
-    const int2 *__restrict__ choice, const uint32_t *__restrict__ chunkEntry, const uint32_t *__restrict__ chunkTok,
-    const uint32_t *__restrict__ chunkBits, const uint32_t *__restrict__ blkSalzLen,
-    const uint64_t *__restrict__ blkOutOff, int framing, int logS, uint32_t totalChunks,
-    uint32_t *__restrict__ tokPos, uint32_t *__restrict__ tokBit, uint32_t *__restrict__ firstTok,
-    uint8_t *__restrict__ out)
-{
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= totalChunks) return;
-    uint32_t e = chunkEntry[c];
-    if (e == NONE) return;
-    const uint32_t b = c >> (logS - PARSE_CHUNK_LOG);
-    const uint32_t N = blkN[b];
-    if (blkSalzLen[b] > N + 4) return;  // PLAIN block
-    const size_t gb = (size_t)b << logS;
-    const uint8_t *Tb = T + (size_t)b * Tstride;
-    uint8_t *ob = out + blkOutOff[b] + (framing ? 4 : 0);
-    uint32_t *tp = tokPos + gb, *tbit = tokBit + gb;
-    uint32_t *ft = firstTok + (gb >> 2);
-    const uint32_t end = min(N, ((e >> PARSE_CHUNK_LOG) + 1) << PARSE_CHUNK_LOG);
-    uint32_t t = chunkTok[c], Bt = chunkBits[c];
-    uint32_t p = e;
-    while (p < end) {
-        int2 ch = choice[gb + p];
-        TokBits tb = token_bits(ch);
-        tp[t] = p;
-        tbit[t] = Bt;
-        uint32_t bytePos = 4 + t + 8 * ((Bt + tb.pre + 63) >> 6);
-        ob[bytePos] = (ch.y == 1) ? Tb[p] : (uint8_t)(((uint32_t)ch.x - 1u) & 0xffu);
-        uint32_t Bn = Bt + tb.pre + tb.post;
-        for (uint32_t k = (Bt + 63) >> 6; k < ((Bn + 63) >> 6); k++) ft[k] = t;
-        Bt = Bn;
-        t++;
-        p += (uint32_t)ch.y;
-    }
-}
-#endif
-
-// One WARP per chunk (default; SALZ_EMIT_WARP=0 launches the one-thread-per-chunk form
-// above).  The thread-per-chunk walk is a chain of ~400 dependent 8-byte loads per thread,
+// One WARP per chunk.  A thread-per-chunk walk (the first form of this kernel) is a chain of ~400 dependent 8-byte loads per thread,
 // 131 K chains each pulling single sectors out of a 2 GB array (1.6 TB/s of DRAM traffic at
 // 5 % issue utilisation), and its per-token stores are scattered across the threads.  Here
 // the warp loads the chunk's chosen lengths coalesced into shared memory (clamped to 16
 // bits: anything longer leaves the chunk anyway), lane 0 walks them there and leaves the
 // list of token positions, and then all lanes handle 32 tokens at a time: bit offsets by a
 // warp scan, tokPos / tokBit written as coalesced runs.  Same stores, same values.
-#if SALZ_EMIT_WARP
 constexpr int EW = 4;   // warps (chunks) per CTA
 __global__ void __launch_bounds__(EW * 32) k_emit_tokens_warp(
     const uint8_t *__restrict__ T, size_t Tstride, const uint32_t *__restrict__ blkN,
@@ -300,7 +253,6 @@ __global__ void __launch_bounds__(EW * 32) k_emit_tokens_warp(
     }
 }
 
-#endif
 
 // ORs the bits of a field into word `w`.  The field covers global bits
 // [s, s+nb) with its least significant bit last; the word covers [w0, w0+64).
@@ -413,15 +365,9 @@ int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,
     k_block_scan<<<bd.B, 256, 0, st>>>(ws.blkN, chunksPerBlock, ws.chunkTok, ws.chunkBits, ws.blkTokens,
                                        ws.blkBits, ws.blkSalzLen, ws.blkOutLen);
     k_out_offsets<<<1, 32, 0, st>>>(ws.blkOutLen, bd.B, framing, ws.blkOutOff);
-#if SALZ_EMIT_WARP
     k_emit_tokens_warp<<<(totalChunks + EW - 1) / EW, EW * 32, 0, st>>>(
         ws.T, bd.Tstride, ws.blkN, ws.choice, ws.chunkEntry, ws.chunkTok, ws.chunkBits, ws.blkSalzLen,
         ws.blkOutOff, framing, bd.logS, totalChunks, ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
-#else
-    k_emit_tokens<<<(totalChunks + 127) / 128, 128, 0, st>>>(
-        ws.T, bd.Tstride, ws.blkN, ws.choice, ws.chunkEntry, ws.chunkTok, ws.chunkBits, ws.blkSalzLen,
-        ws.blkOutOff, framing, bd.logS, totalChunks, ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
-#endif
     k_emit_words<<<(uint32_t)((total >> 2) / 256), 256, 0, st>>>(ws.blkN, ws.choice, ws.blkTokens, ws.blkBits,
                                                                  ws.blkSalzLen, ws.blkOutOff, framing, bd.logS,
                                                                  ws.tokPos, ws.tokBit, ws.firstTok, ws.out);
@@ -429,6 +375,7 @@ int emit_build(Workspace &ws, const BatchDesc &bd, int framing, cudaStream_t st,
     k_finalize<<<fg, 256, 0, st>>>(ws.T, bd.Tstride, ws.blkN, ws.blkSalzLen, ws.blkOutLen, ws.blkOutOff, framing,
                                    ws.out);
     lc.launches += 7;
+    lc.alg_bytes += (uint64_t)bd.M * 29;   // + the output bytes, added by the caller once the sizes are known
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "salz_cuda: emit_build: %s\n", cudaGetErrorString(e));

@@ -271,6 +271,7 @@ int lcp_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCounter
     k_plcp_scan_tiles<<<bd.B, 256, 0, st>>>(ws.tileMax, tilesPerBlock);
     k_plcp_apply<<<tiles, LT, 0, st>>>(ws.blkN, ws.rank, bd.logS, ws.tileMax, ws.plcp, ws.lcp);
     lc.launches += 3;
+    lc.alg_bytes += (uint64_t)bd.M * (17 + 20);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         fprintf(stderr, "salz_cuda: lcp_build: %s\n", cudaGetErrorString(e));

@@ -500,10 +500,13 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
                                                                                  ws.segBase);
             k_seg_scan<<<(bd.B + 63) / 64, 64, 0, st>>>(ws.blkN, bd.B, bd.logS, segLog, cur, ws.segBase);
             lc.launches += 2;
+            // first pass with a warm-up window walks `warm` chunks of every segment only
+            lc.alg_bytes += (pass == 1 && warm) ? (uint64_t)chains * warm * PC * 20 : (uint64_t)bd.M * 20;
             if (pass >= 2) {
                 if (cudaMemsetAsync(ws.counters + 9, 0, 4, st) != cudaSuccess) return -1;
                 k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.jump, ws.counters);
                 lc.launches += 1;
+                lc.alg_bytes += (uint64_t)bd.M * 32;
                 if (cudaMemcpyAsync(ws.h_counters + 9, ws.counters + 9, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
                 if (cudaStreamSynchronize(st) != cudaSuccess) return -1;
                 done = ws.h_counters[9] == 0;
@@ -523,6 +526,7 @@ int parse_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, LaunchCount
                                                                            0u, ws.numSMs, cur, old, ws.segBase);
         k_choose<<<chooseGrid, 256, 0, st>>>(ws.cand, ws.blkN, bd.logS, segLog, cur, ws.segBase, ws.choice, ws.jump, ws.counters);
         lc.launches += 2;
+        lc.alg_bytes += (uint64_t)bd.M * (20 + 32);
     }
     ws.parseSegLog = segLog;
     ws.parseDr = cur;

@@ -901,9 +901,6 @@ __global__ void __launch_bounds__(256) k_sched(const uint32_t *__restrict__ tile
 // changes); the SA slot of element k is  group(k) + (k - index of its pst),
 // and the new group id is the slot of the element's head.
 
-#ifndef SALZ_RERANK_FUSED
-#define SALZ_RERANK_FUSED 1
-#endif
 struct HK { uint32_t head, pst, keep; };  // head/pst: list index + 1 of the last flagged element (0 none)
 
 __device__ __forceinline__ HK hk_combine(HK a, HK b)
@@ -999,85 +996,6 @@ __device__ __forceinline__ void load_flags(const uint64_t *__restrict__ keys, co
 __device__ __forceinline__ int rr_phys(int x) { return x + x / ITEMS; }
 constexpr int RR_STAGE = TILE + 2 + (TILE + 2) / ITEMS + 1;
 
-#if !SALZ_RERANK_FUSED
-template <bool PACKED, bool ROUND0>
-__global__ void __launch_bounds__(TT) k_rerank_reduce(const uint64_t *__restrict__ keys, ListView lv, int logS,
-                                                      uint32_t *__restrict__ aggHead, uint32_t *__restrict__ aggPst,
-                                                      uint32_t *__restrict__ aggKeep)
-{
-    __shared__ HK scratch[WARPS + 1];
-    const TileLoc tl = locate(lv, blockIdx.x);
-    const uint32_t segRemain = lv.cnt[tl.b] - tl.lt * TILE;
-    const uint32_t i0 = threadIdx.x * ITEMS;
-    uint64_t e[ITEMS];
-    bool head[ITEMS + 1], pst[ITEMS];
-    load_flags<PACKED, ROUND0>(keys, tl, segRemain, i0, logS, e, head, pst);
-    HK v = {0, 0, 0};
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        if (i0 + i < tl.valid) {
-            const uint32_t k = tl.first + i0 + i;
-            if (head[i]) v.head = k + 1;
-            if (pst[i]) v.pst = k + 1;
-            if (!(head[i] && head[i + 1])) v.keep++;
-        }
-    }
-    HK agg;
-    hk_block_excl(v, &agg, scratch);
-    if (threadIdx.x == 0) {
-        aggHead[blockIdx.x] = agg.head;
-        aggPst[blockIdx.x] = agg.pst;
-        aggKeep[blockIdx.x] = agg.keep;
-    }
-}
-
-// Single CTA: exclusive scan of the tile aggregates, in place.
-__global__ void __launch_bounds__(1024) k_rerank_scan(uint32_t *__restrict__ aggHead, uint32_t *__restrict__ aggPst,
-                                                      uint32_t *__restrict__ aggKeep, uint32_t tiles)
-{
-    __shared__ HK part[1024];
-    const int tid = threadIdx.x;
-    const uint32_t per = (tiles + 1023) / 1024;
-    const uint32_t lo = min(tiles, tid * per), hi = min(tiles, lo + per);
-    HK s = {0, 0, 0};
-    for (uint32_t t = lo; t < hi; t++) s = hk_combine(s, HK{aggHead[t], aggPst[t], aggKeep[t]});
-    part[tid] = s;
-    __syncthreads();
-    if (tid < 32) {
-        HK a = {0, 0, 0};
-        for (int i = 0; i < 32; i++) a = hk_combine(a, part[tid * 32 + i]);
-        HK inc = a;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            HK t;
-            t.head = __shfl_up_sync(0xffffffffu, inc.head, o);
-            t.pst = __shfl_up_sync(0xffffffffu, inc.pst, o);
-            t.keep = __shfl_up_sync(0xffffffffu, inc.keep, o);
-            if (tid >= o) inc = hk_combine(t, inc);
-        }
-        HK run;
-        run.head = __shfl_up_sync(0xffffffffu, inc.head, 1);
-        run.pst = __shfl_up_sync(0xffffffffu, inc.pst, 1);
-        run.keep = __shfl_up_sync(0xffffffffu, inc.keep, 1);
-        if (tid == 0) run = HK{0, 0, 0};
-        for (int i = 0; i < 32; i++) {
-            HK c = part[tid * 32 + i];
-            part[tid * 32 + i] = run;
-            run = hk_combine(run, c);
-        }
-    }
-    __syncthreads();
-    s = part[tid];
-    for (uint32_t t = lo; t < hi; t++) {
-        HK c = {aggHead[t], aggPst[t], aggKeep[t]};
-        aggHead[t] = s.head;
-        aggPst[t] = s.pst;
-        aggKeep[t] = s.keep;
-        s = hk_combine(s, c);
-    }
-}
-#endif
-
 // Tile state of the single-pass re-rank (decoupled look-back inside a block's tiles): one
 // 16-byte word per tile, written and read whole (x = head | pst << 32, y = keep | status << 32).
 constexpr uint32_t RR_AGG = 1, RR_PREFIX = 2;
@@ -1142,9 +1060,7 @@ __device__ __forceinline__ HK rr_lookback(ulonglong2 *state, uint32_t tile, uint
 
 template <bool PACKED, bool ROUND0>
 __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
-                                                     ListView lv, int logS, const uint32_t *__restrict__ aggHead,
-                                                     const uint32_t *__restrict__ aggPst,
-                                                     const uint32_t *__restrict__ aggKeep, uint32_t round,
+                                                     ListView lv, int logS, uint32_t round,
                                                      uint64_t *__restrict__ rank, uint32_t *__restrict__ SA,
                                                      uint64_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut,
                                                      const uint32_t *__restrict__ cntBefore,
@@ -1208,20 +1124,15 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
     };
     HK ex;
     uint32_t keepBase;  // survivors of the block's earlier tiles
-    if (lookState) {    // single pass: the prefix over the block's earlier tiles by look-back
-        if (threadIdx.x < 32) {
-            const HK pre = rr_lookback(lookState, blockIdx.x, tl.lt, agg, (int)threadIdx.x);
-            if (threadIdx.x == 0) tilePrefix = pre;
-        }
-        early();   // warp 0 after its look-back, the other warps while it waits
-        __syncthreads();
-        ex = hk_combine(tilePrefix, exLoc);
-        keepBase = 0;
-    } else {
-        early();
-        ex = hk_combine(HK{aggHead[blockIdx.x], aggPst[blockIdx.x], aggKeep[blockIdx.x]}, exLoc);
-        keepBase = aggKeep[lv.tileBase[tl.b]];
+    // the prefix over the block's earlier tiles by look-back
+    if (threadIdx.x < 32) {
+        const HK pre = rr_lookback(lookState, blockIdx.x, tl.lt, agg, (int)threadIdx.x);
+        if (threadIdx.x == 0) tilePrefix = pre;
     }
+    early();   // warp 0 after its look-back, the other warps while it waits
+    __syncthreads();
+    ex = hk_combine(tilePrefix, exLoc);
+    keepBase = 0;
     if (threadIdx.x == 0 && agg.keep) atomicAdd(&cntNext[tl.b], agg.keep);
     // survivors are appended, in list order, behind what the block's next list already
     // holds (cntBefore: a snapshot taken before this launch; null = nothing); packed
@@ -1703,24 +1614,13 @@ int rerank(SortCtx &s, int v, uint32_t count, uint32_t tiles, int src, int dst, 
     Workspace &ws = s.ws;
     const int logS = s.bd.logS;
     const ListView lv = view(ws, v);
-#if SALZ_RERANK_FUSED
     // single pass: tile prefixes by look-back (the scatter passes' tile state is free by now)
     ulonglong2 *look = (ulonglong2 *)ws.tileState;
     CK(cudaMemsetAsync(look, 0, (size_t)tiles * sizeof(ulonglong2), s.st));
-    k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, ws.aggHead, ws.aggPst,
-                                                           ws.aggKeep, round, ws.rank, ws.SA, ws.keys[dst],
+    k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, round, ws.rank, ws.SA, ws.keys[dst],
                                                            ws.vals[dst & 1], cntBefore, ws.listCnt[vNext], look);
     s.lc.launches += 1;
     s.algBytes += (uint64_t)count * (PACKED ? 20 : 28);
-#else
-    k_rerank_reduce<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], lv, logS, ws.aggHead, ws.aggPst, ws.aggKeep);
-    k_rerank_scan<<<1, 1024, 0, s.st>>>(ws.aggHead, ws.aggPst, ws.aggKeep, tiles);
-    k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, ws.aggHead, ws.aggPst,
-                                                           ws.aggKeep, round, ws.rank, ws.SA, ws.keys[dst],
-                                                           ws.vals[dst & 1], cntBefore, ws.listCnt[vNext], nullptr);
-    s.lc.launches += 3;
-    s.algBytes += (uint64_t)count * (PACKED ? 28 : 36);
-#endif
     CK(cudaGetLastError());
     if (dbg(s, "rerank")) return -1;
     return 0;

@@ -56,10 +56,6 @@ struct Workspace {
     uint32_t *passDone;  // [Bmax][8] tiles that have finished (block, pass) in that launch
     int scatterMode;     // 0 = register-staged k_scatter, 1 = TMA-staged, 2 = TMA-staged + two keys per ranking step
     int sortGroup;       // > 0: all passes of a sort in one launch, block groups of this many blocks (L2-resident)
-    // rerank scans
-    uint32_t *aggHead;  // [tileCap]
-    uint32_t *aggPst;   // [tileCap]
-    uint32_t *aggKeep;  // [tileCap]
     uint32_t *counters; // [16] device scalars: [0]=list length, [1]=tiles
     uint32_t *h_counters; // pinned mirror
     uint32_t *h_blkN;     // pinned host copy of blkN (owned by the context)
@@ -224,7 +220,13 @@ __device__ __forceinline__ int32_t ld_stream(const int32_t *a, uint64_t pol)
 }
 
 // ---- host-side launchers (one per pipeline stage) --------------------------
-struct LaunchCounter { uint64_t launches, sort_launches, sort_elems, sort_bytes; };
+// alg_bytes: algorithmic HBM bytes of the stages after the suffix array, counted where the
+// kernels are launched (per position of the batch, M = sum of n_b):
+//   k_plcp_irreducible  rank 8 + SA 4 + text ~1 + V 4 = 17      k_plcp_apply  V 4 + rank 8 + PLCP 4 + LCP 4 = 20
+//   k_ansv_tile         SA 4 + LCP 4 + candidates 16 = 24        (far items, pyramids: < 1)
+//   k_parse             candidates 16 + d 4 per position walked  k_choose  candidates 16 + d 4 + choice 8 + jump 4 = 32
+//   emit                choice 8 (walk) + choice 8, text 1, tokPos/tokBit 8 (tokens) + ~4 (words) + output
+struct LaunchCounter { uint64_t launches, sort_launches, sort_elems, sort_bytes, alg_bytes; };
 
 // sa.cu
 int sa_tile_elems();  // list elements per sort tile
