@@ -8,8 +8,8 @@ while IFS= read -r line; do
   [ -z "$line" ] && continue
   [ "$line" = "-" ] && line=""
   echo "=== ${line:-defaults}"
-  env $line timeout 600 python -m pytest tests/test_gpu.py -m gpu -x -q -k "medium or small or batched or alphabet" 2>&1 | tail -1
-  env $line timeout 600 python bench.py --steps 3 --warmup 2 --no-cpu-baseline --no-e2e $* 2>&1 | python -c "
+  env $line timeout 120 python -m pytest tests/test_gpu.py -m gpu -x -q -k "medium or small or batched or alphabet" 2>&1 | tail -1
+  env $line timeout 180 python bench.py --steps 3 --warmup 2 --no-cpu-baseline --no-e2e --no-extras $* 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):

@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 for args in "--level 1 --batch-blocks 2048" "--level 3 --batch-blocks 1024" "--level 4" "--level 7"; do
   echo "=== $args"
-  timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline $args 2>&1 | python -c "
+  timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras $args 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):

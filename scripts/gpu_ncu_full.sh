@@ -3,7 +3,7 @@
 # exported to CSV on the box (raw metrics for every launch of the main kernels; source view of a
 # few) and removed, so that gpurun_out/ stays under its size limit.
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e"
+CMD="python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-extras --no-e2e"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu0.log 2>&1
 echo "ncu0 exit $?"

@@ -5,7 +5,7 @@ for v in variants/*.so; do
   cp $v salz_b200/libsalz_cuda.so
   echo "=== $v"
   timeout 600 python -m pytest tests/test_gpu.py -m gpu -x -q -k "medium or small or batched" 2>&1 | tail -1
-  timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e $* 2>&1 | python -c "
+  timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras --no-e2e $* 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):

@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 for args in "--workload dna1g --batch-blocks 512" "--workload single512 --batch-blocks 512" "--workload random512 --batch-blocks 512" "--workload english256 --level 9" "--workload single512 --level 9 --mib 128"; do
   echo "=== $args"
-  timeout 900 python bench.py --steps 2 --warmup 1 --no-cpu-baseline $args 2>&1 | python -c "
+  timeout 900 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras $args 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
