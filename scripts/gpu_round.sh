@@ -1,12 +1,12 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, bench line, ncu launch list.  Output in gpurun_out/.
+# One GPU-box visit: parity tests, bench line (all extras).  Output in gpurun_out/.
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
-nproc >> gpurun_out/gpu.txt; grep -m1 "model name" /proc/cpuinfo >> gpurun_out/gpu.txt
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1
+nproc >> gpurun_out/gpu.txt; grep -m1 "model name" /proc/cpuinfo >> gpurun_out/gpu.txt; free -g | head -2 >> gpurun_out/gpu.txt
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
 tail -5 gpurun_out/pytest_gpu.log
-timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err
+/usr/bin/time -v timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err
 echo "bench exit $?"
-cat gpurun_out/bench.json
-tail -3 gpurun_out/bench.err
+cut -c1-3000 gpurun_out/bench.json
+grep -i "elapsed\|error\|Traceback" gpurun_out/bench.err | head; tail -3 gpurun_out/bench.err
