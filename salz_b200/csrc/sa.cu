@@ -1323,47 +1323,124 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     }
     if (s_misc[2] >= s_misc[3]) return;
 
-    hi -= lo;
-    lo = 0;
-    // sort the window by (group, second, p): blocked registers, network, merges
+    // ---- order the window's own groups [lo, hi) by (group, second, p) ----
+    // The groups are already in place, so only the order INSIDE each group is missing.
+    // Small groups (most of them; all of them in late rounds and on repeat-rich input): every
+    // element counts the smaller keys of its own group and goes straight to its slot - a
+    // few shared-memory loads per element where the merge sort below spends ~200 thread
+    // instructions.  Only when the window holds a group larger than SMALL_GROUP does the
+    // network + merge-path sort run, and then small groups are already in order, so most
+    // of its run pairs are skipped.
+    constexpr int SMALL_GROUP = 32;
+    const int cnt = hi - lo;
     uint64_t k[LITEMS];
+    const int j0 = tid * LITEMS;
 #pragma unroll
-    for (int i = 0; i < LITEMS; i++) k[i] = sk[lphys(tid * LITEMS + i)];
-    sort_network<LITEMS>(k);
+    for (int i = 0; i < LITEMS; i++) k[i] = (j0 + i < cnt) ? sk[lphys(lo + j0 + i)] : ~0ull;
+    uint16_t *gsize = (uint16_t *)sh;   // [W] size of the group that starts at an index (the histogram is flushed)
+    {
+        // start of the group of each of my elements: heads inside my range, else the last head before it
+        const uint32_t gPrev = (j0 > 0 && j0 <= cnt) ? (uint32_t)(sk[lphys(lo + j0 - 1)] >> (2 * logS)) : 0xffffffffu;
+        uint32_t headBits = 0;
+        uint32_t pg = gPrev;
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const uint32_t g = (uint32_t)(k[i] >> (2 * logS));
+            if (j0 + i < cnt && (j0 + i == 0 || g != pg)) headBits |= 1u << i;
+            pg = g;
+        }
+        // exclusive max-scan over the threads of (index of my last head + 1)
+        uint32_t v = headBits ? (uint32_t)(j0 + 31 - __clz(headBits)) + 1u : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) inc = max(inc, __shfl_up_sync(0xffffffffu, inc, o));
+        if (lane == 31) swarp[warp].head = inc;
+        __syncthreads();   // also: every thread has its elements in registers
+        uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1);
+        if (lane == 0) exc = 0;
+        for (int w = 0; w < warp; w++) exc = max(exc, swarp[w].head);
+        // sizes: a head closes the group before it; the end of the window closes the last one
+        uint32_t start = exc ? exc - 1u : 0u;
+        uint32_t starts[LITEMS / 2];   // two 16-bit group starts per register
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = j0 + i;
+            if ((headBits >> i) & 1u) {
+                if (j > 0) gsize[start] = (uint16_t)(j - (int)start);
+                start = (uint32_t)j;
+            }
+            if (j == cnt - 1) gsize[start] = (uint16_t)(cnt - (int)start);
+            if (i & 1) starts[i >> 1] |= start << 16; else starts[i >> 1] = start;
+        }
+        __syncthreads();
+        bool large = false;
+        uint32_t dest[LITEMS / 2];
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = j0 + i;
+            uint32_t d = (uint32_t)j;
+            if (j < cnt) {
+                const uint32_t gs = (starts[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+                const uint32_t sz = gsize[gs];
+                if (sz > (uint32_t)SMALL_GROUP) {
+                    large = true;
+                } else if (sz > 1) {
+                    uint32_t r = 0;
+                    for (uint32_t q = 0; q < sz; q++) r += (sk[lphys(lo + (int)(gs + q))] < k[i]) ? 1u : 0u;
+                    d = gs + r;
+                }
+            }
+            if (i & 1) dest[i >> 1] |= d << 16; else dest[i >> 1] = d;
+        }
+        const int anyLarge = __syncthreads_or(large ? 1 : 0);   // all reads of the old layout are done
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) sk[lphys((int)((dest[i >> 1] >> (16 * (i & 1))) & 0xffffu))] = k[i];
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) k[i] = sk[lphys(j0 + i)];
+        hi = cnt;
+        lo = 0;
+        if (anyLarge) {
+            // network + merges; a thread whose elements are in order already skips the network
+            bool ordered = true;
+#pragma unroll
+            for (int i = 0; i + 1 < LITEMS; i++) ordered = ordered && (k[i] <= k[i + 1]);
+            if (!ordered) sort_network<LITEMS>(k);
 #pragma unroll 1
-    for (int width = 1; width < LT; width <<= 1) {
-        __syncthreads();
+            for (int width = 1; width < LT; width <<= 1) {
+                __syncthreads();
 #pragma unroll
-        for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
-        __syncthreads();
-        const int pairFirst = tid & ~(2 * width - 1);
-        const int aBeg = pairFirst * LITEMS, bBeg = aBeg + width * LITEMS, bEnd = bBeg + width * LITEMS;
-        if (sk[lphys(bBeg - 1)] > sk[lphys(bBeg)]) {   // otherwise the two runs are already in order
-            const int diag = (tid - pairFirst) * LITEMS;
-            const int len = width * LITEMS;
-            int a = max(0, diag - len), b = min(diag, len);
-            while (a < b) {
-                const int m = (a + b) >> 1;
-                if (sk[lphys(aBeg + m)] <= sk[lphys(bBeg + diag - 1 - m)]) a = m + 1; else b = m;
-            }
-            int ai = aBeg + a, bi = bBeg + diag - a;
-            uint64_t ka = sk[lphys(ai)], kb = sk[lphys(min(bi, W - 1))];
+                for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
+                __syncthreads();
+                const int pairFirst = tid & ~(2 * width - 1);
+                const int aBeg = pairFirst * LITEMS, bBeg = aBeg + width * LITEMS, bEnd = bBeg + width * LITEMS;
+                if (sk[lphys(bBeg - 1)] > sk[lphys(bBeg)]) {   // otherwise the two runs are already in order
+                    const int diag = (tid - pairFirst) * LITEMS;
+                    const int len = width * LITEMS;
+                    int a = max(0, diag - len), b = min(diag, len);
+                    while (a < b) {
+                        const int m = (a + b) >> 1;
+                        if (sk[lphys(aBeg + m)] <= sk[lphys(bBeg + diag - 1 - m)]) a = m + 1; else b = m;
+                    }
+                    int ai = aBeg + a, bi = bBeg + diag - a;
+                    uint64_t ka = sk[lphys(ai)], kb = sk[lphys(min(bi, W - 1))];
 #pragma unroll
-            for (int i = 0; i < LITEMS; i++) {
-                const bool takeB = (bi < bEnd) && (ai >= bBeg || kb < ka);
-                k[i] = takeB ? kb : ka;
-                if (takeB) { bi++; kb = sk[lphys(min(bi, W - 1))]; }
-                else { ai++; ka = sk[lphys(min(ai, W - 1))]; }
+                    for (int i = 0; i < LITEMS; i++) {
+                        const bool takeB = (bi < bEnd) && (ai >= bBeg || kb < ka);
+                        k[i] = takeB ? kb : ka;
+                        if (takeB) { bi++; kb = sk[lphys(min(bi, W - 1))]; }
+                        else { ai++; ka = sk[lphys(min(ai, W - 1))]; }
+                    }
+                }
             }
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
+            __syncthreads();
         }
     }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
-    __syncthreads();
 
     // re-rank inside the window: flags, scan, new group ids
-    const int j0 = tid * LITEMS;
     uint64_t prevKf = (j0 > 0) ? (sk[lphys(j0 - 1)] >> logS) : 0;
     const uint64_t nextKf = (j0 + LITEMS < W) ? (sk[lphys(j0 + LITEMS)] >> logS) : ~0ull;
     const uint64_t secMask = ((uint64_t)1 << logS) - 1;
