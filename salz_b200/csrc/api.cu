@@ -110,8 +110,10 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ws.S = 1u << logS;
     ws.Bmax = max_batch_blocks;
     ws.Mcap = ws.Bmax * (size_t)ws.S;
-    if (ws.Mcap > ((size_t)1 << 30)) {
-        fprintf(stderr, "salz_cuda: batch of %zu x %u exceeds 2^30 positions\n", ws.Bmax, ws.S);
+    // 32-bit slot indices everywhere; ~90 B of workspace per position: 2^30 + 2^27 positions
+    // (the 1 GiB + 4096 B inputs of BASELINE.json in ONE batch) take ~105 GB of the 180 GB
+    if (ws.Mcap > ((size_t)1 << 30) + ((size_t)1 << 27)) {
+        fprintf(stderr, "salz_cuda: batch of %zu x %u exceeds 2^30 + 2^27 positions\n", ws.Bmax, ws.S);
         delete c;
         return nullptr;
     }

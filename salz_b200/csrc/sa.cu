@@ -368,11 +368,22 @@ __global__ void __launch_bounds__(TT) k_build(const uint64_t *__restrict__ rank,
 }
 
 // digitBase[b][pass][d] = exclusive scan of hist[b][pass][*].  grid = (passes, B)
-__global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digitBase)
+// identMask (optional): bit `pass` is cleared unless ONE digit holds every element of the
+// block's list in that pass.  A pass whose bit survives for all blocks is the identity
+// permutation (LSD passes are stable) and the host leaves it out - the passes over the group
+// bits of a list that holds a single group per block (a run of one byte: SURVEY H3).
+__global__ void __launch_bounds__(256) k_scan_hist(const uint32_t *__restrict__ hist, uint32_t *__restrict__ digitBase,
+                                                   const uint32_t *__restrict__ listCnt, uint32_t *identMask)
 {
     __shared__ uint32_t scratch[16];
     const size_t o = ((size_t)blockIdx.y * MAXP + blockIdx.x) * 256 + threadIdx.x;
-    digitBase[o] = excl_scan_first256(hist[o], scratch);
+    const uint32_t h = hist[o];
+    digitBase[o] = excl_scan_first256(h, scratch);
+    if (identMask) {
+        const uint32_t total = listCnt[blockIdx.y];
+        const int one = __syncthreads_or(h == total);
+        if (!one && threadIdx.x == 0) atomicAnd(identMask, ~(1u << blockIdx.x));
+    }
 }
 
 // ---- the radix scatter pass -------------------------------------------------------
@@ -1373,28 +1384,39 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             if (i & 1) starts[i >> 1] |= start << 16; else starts[i >> 1] = start;
         }
         __syncthreads();
+        // Does the window hold a group larger than SMALL_GROUP?  Then the merge sort runs anyway
+        // and the counting would be extra work (text, early rounds); otherwise counting alone
+        // orders the window (late rounds; repeat-rich input, where every group is a pair).
         bool large = false;
-        uint32_t dest[LITEMS / 2];
 #pragma unroll
-        for (int i = 0; i < LITEMS; i++) {
-            const int j = j0 + i;
-            uint32_t d = (uint32_t)j;
-            if (j < cnt) {
-                const uint32_t gs = (starts[i >> 1] >> (16 * (i & 1))) & 0xffffu;
-                const uint32_t sz = gsize[gs];
-                if (sz > (uint32_t)SMALL_GROUP) {
-                    large = true;
-                } else if (sz > 1) {
-                    uint32_t r = 0;
-                    for (uint32_t q = 0; q < sz; q++) r += (sk[lphys(lo + (int)(gs + q))] < k[i]) ? 1u : 0u;
-                    d = gs + r;
+        for (int i = 0; i < LITEMS; i++)
+            if ((headBits >> i) & 1u) large = large || gsize[j0 + i] > (uint32_t)SMALL_GROUP;
+        const int anyLarge = __syncthreads_or(large ? 1 : 0);
+        if (!anyLarge) {
+            uint32_t dest[LITEMS / 2];
+#pragma unroll
+            for (int i = 0; i < LITEMS; i++) {
+                const int j = j0 + i;
+                uint32_t d = (uint32_t)j;
+                if (j < cnt) {
+                    const uint32_t gs = (starts[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+                    const uint32_t sz = gsize[gs];
+                    if (sz > 1) {
+                        uint32_t r = 0;
+                        for (uint32_t q = 0; q < sz; q++) r += (sk[lphys(lo + (int)(gs + q))] < k[i]) ? 1u : 0u;
+                        d = gs + r;
+                    }
                 }
+                if (i & 1) dest[i >> 1] |= d << 16; else dest[i >> 1] = d;
             }
-            if (i & 1) dest[i >> 1] |= d << 16; else dest[i >> 1] = d;
-        }
-        const int anyLarge = __syncthreads_or(large ? 1 : 0);   // all reads of the old layout are done
+            __syncthreads();   // all reads of the old layout are done
 #pragma unroll
-        for (int i = 0; i < LITEMS; i++) sk[lphys((int)((dest[i >> 1] >> (16 * (i & 1))) & 0xffffu))] = k[i];
+            for (int i = 0; i < LITEMS; i++) sk[lphys((int)((dest[i >> 1] >> (16 * (i & 1))) & 0xffffu))] = k[i];
+        } else {
+            // shifted to the front of the window, padding behind (every element is in registers)
+#pragma unroll
+            for (int i = 0; i < LITEMS; i++) sk[lphys(j0 + i)] = k[i];
+        }
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < LITEMS; i++) k[i] = sk[lphys(j0 + i)];
@@ -1599,7 +1621,7 @@ void tilemap(SortCtx &s, int v, uint32_t tileElems, int slot)
 
 int fetch_counters(SortCtx &s)
 {
-    CK(cudaMemcpyAsync(s.ws.h_counters, s.ws.counters, 16, cudaMemcpyDeviceToHost, s.st));
+    CK(cudaMemcpyAsync(s.ws.h_counters, s.ws.counters, 64, cudaMemcpyDeviceToHost, s.st));
     CK(cudaStreamSynchronize(s.st));
     return 0;
 }
@@ -1607,15 +1629,17 @@ int fetch_counters(SortCtx &s)
 // `passes` LSD passes over list view `v` (count elements in `tiles` tiles), starting
 // in keys[src]; the other buffer is keys[dst].  Returns the buffer holding the result.
 template <bool PACKED>
-int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, int shift0, int src, int dst)
+int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, int shift0, int src, int dst,
+               uint32_t skipMask = 0)
 {
     Workspace &ws = s.ws;
+    int done = 0;   // passes actually run (skipMask: passes that are the identity for every block)
     if (s.msSort) CK(cudaEventRecord(s.evA, s.st));
     if (PACKED && ws.scatterMode > 0) {
         // TMA-staged kernel.  sortGroup > 0: all passes in ONE launch, tickets block-group-major
         // (a group's lists stay in L2 from pass to pass); otherwise a launch per pass.
         const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SALZ_TCTAS));
-        const bool fused = ws.sortGroup > 0 && passes > 1;
+        const bool fused = ws.sortGroup > 0 && passes > 1 && skipMask == 0;
         CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
         if (fused) {
             const uint32_t tickets = tiles * (uint32_t)passes;
@@ -1628,10 +1652,12 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
                 k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
             s.lc.launches += 2;
             s.lc.sort_launches += 1;
+            done = passes;
             if (passes & 1) std::swap(src, dst);
         } else {
             for (int ps = 0; ps < passes; ps++) {
-                if (ps) CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
+                if ((skipMask >> ps) & 1u) continue;
+                if (done) CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
                 const PassPlan pp = {nullptr, tiles, ps, shift0 + 8 * ps, nullptr};
                 if (ws.scatterMode == 2)
                     k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
@@ -1639,15 +1665,18 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
                     k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
                 s.lc.launches += 1;
                 s.lc.sort_launches += 1;
+                done++;
                 std::swap(src, dst);
             }
         }
-        s.lc.sort_elems += (uint64_t)count * passes;
-        s.lc.sort_bytes += (uint64_t)count * 16 * passes;
+        s.lc.sort_elems += (uint64_t)count * done;
+        s.lc.sort_bytes += (uint64_t)count * 16 * done;
     } else {
         const size_t smem = PACKED ? SCATTER_SMEM_PACKED : SCATTER_SMEM_PAIRS;
         const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SCATTER_MIN_CTAS));
         for (int ps = 0; ps < passes; ps++) {
+            if ((skipMask >> ps) & 1u) continue;
+            done++;
             CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
             if (s.matchAny)
                 k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst], ws.vals[dst & 1],
@@ -1666,7 +1695,7 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
     }
     if (s.msSort) CK(cudaEventRecord(s.evB, s.st));
     CK(cudaGetLastError());
-    s.algBytes += (uint64_t)count * (PACKED ? 16 : 24) * passes;
+    s.algBytes += (uint64_t)count * (PACKED ? 16 : 24) * done;
     if (dbg(s, "radix_sort")) return -1;
     return src;
 }
@@ -1734,7 +1763,7 @@ int round0(SortCtx &s, int passes, int shift0, int vNext, int *bufOut)
     CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
     k_init<PACKED><<<tiles, TT, 0, s.st>>>(ws.T, bd.Tstride, ws.blkN, view(ws, 2), logS, passes, ws.codeTab, ws.symBits,
                                            ws.h0, ws.keys[0], ws.vals[0], ws.hist);
-    k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+    k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase, nullptr, nullptr);
     s.lc.launches += 3;
     s.algBytes += (uint64_t)bd.M * (PACKED ? 9 : 13);
     if (dbg(s, "k_init")) return -1;
@@ -1782,12 +1811,15 @@ int sa_build_local(SortCtx &s, int &rounds)
         if (dbg(s, "k_local")) return -1;
         tilemap(s, vNext, LTILE, 0);
         tilemap(s, 2, TILE, 1);
+        // digit bases of the global list, and which of its passes are the identity everywhere
+        CK(cudaMemsetAsync(ws.counters + 12, 0xff, 4, s.st));
+        k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase, ws.listCnt[2], ws.counters + 12);
+        s.lc.launches += 1;
         if (fetch_counters(s)) return -1;
         const uint32_t countL = ws.h_counters[2], tilesL = ws.h_counters[3];
         if (countL > 0) {
-            k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
-            s.lc.launches += 1;
-            const int res = radix_sort<true>(s, 2, countL, tilesL, passes, logS, bufL, bufS);
+            const uint32_t skip = ws.h_counters[12] & ((1u << passes) - 1u);
+            const int res = radix_sort<true>(s, 2, countL, tilesL, passes, logS, bufL, bufS, skip);
             if (res < 0) return -1;
             CK(cudaMemcpyAsync(ws.cntSnap, ws.listCnt[vNext], (size_t)bd.B * 4, cudaMemcpyDeviceToDevice, s.st));
             if (rerank<true, false>(s, 2, countL, tilesL, res, bufOut, round, ws.cntSnap, vNext)) return -1;
@@ -1831,7 +1863,7 @@ int sa_build_pairs(SortCtx &s, int &rounds)
         CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
         k_build<false><<<tiles, TT, 0, s.st>>>(ws.rank, ws.blkN, view(ws, v), logS, ws.h0, round, passes, ws.keys[cur],
                                                ws.vals[cur], ws.hist);
-        k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase);
+        k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase, nullptr, nullptr);
         s.lc.launches += 2;
         s.algBytes += (uint64_t)count * 28;
         const int res = radix_sort<false>(s, v, count, tiles, passes, 0, cur, cur ^ 1);
