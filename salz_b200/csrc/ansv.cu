@@ -77,12 +77,26 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     // kept in L2 (evict_last) until the other pieces arrive; SA and LCP stream through
     const uint64_t keep = l2_evict_last(), stream = l2_evict_first();
 
-    for (int j = tid; j < ATS; j += AT) {
-        const uint32_t r = t0 + j;
-        const int k = (j >> 5) * APAD + (j & 31);
-        if (r < n) {
-            sv[k] = ld_stream(SA + gb + r, stream) << 8;
-            sm[k] = ld_stream(LCP + gb + r, stream);
+    // tile load, eight slots per thread at a time: the loads of a batch are all in flight before
+    // the first of them is used (one load per loop iteration exposed the DRAM latency 32 times:
+    // 23 % of this kernel's stall samples sat on the first use, profiles/r01_v15_ncu_stalls.txt)
+    constexpr int LDB = 8;
+#pragma unroll 1
+    for (int base = 0; base < AL; base += LDB) {
+        uint32_t a[LDB];
+        int32_t l[LDB];
+#pragma unroll
+        for (int u = 0; u < LDB; u++) {
+            const uint32_t r = t0 + (uint32_t)((base + u) * AT + tid);
+            a[u] = (r < n) ? ld_stream(SA + gb + r, stream) : 0u;
+            l[u] = (r < n) ? ld_stream(LCP + gb + r, stream) : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < LDB; u++) {
+            const int j = (base + u) * AT + tid;
+            const int k = (j >> 5) * APAD + (j & 31);
+            sv[k] = a[u] << 8;
+            sm[k] = l[u];
         }
     }
     __syncthreads();

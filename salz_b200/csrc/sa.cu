@@ -1108,7 +1108,6 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
     HK agg;
     const HK exLoc = hk_block_excl(v, &agg, scratch);   // exclusive inside the tile
     const size_t gb = (size_t)tl.b << logS;
-    const uint64_t keep = l2_evict_last();   // rank / SA scatters: partial sectors wait in L2 for their neighbours
     // Round 0: the one pst of a segment is its first element, whatever the tile.
     const uint32_t pst0 = tl.first - tl.lt * TILE + 1;
     // Elements whose head (and pst) lie inside the tile do not need the prefix over the
@@ -1127,8 +1126,8 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
                     if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
                     else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
                     const uint32_t r = prim + (curHead - curPst);
-                    st_hint(&rank[gb + p], rk_make(round, prim, r), keep);
-                    if (head[i] && head[i + 1]) st_hint(&SA[gb + r], p, keep);
+                    rank[gb + p] = rk_make(round, prim, r);
+                    if (head[i] && head[i + 1]) SA[gb + r] = p;
                 }
             }
         }
@@ -1163,9 +1162,9 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
             if (PACKED) { p = (uint32_t)e[i] & Smask; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> (2 * logS)); }
             else { p = vals[k]; prim = ROUND0 ? 0u : (uint32_t)(e[i] >> logS); }
             const uint32_t r = prim + (curHead - curPst);  // SA slot of the group head
-            if (!done) st_hint(&rank[gb + p], rk_make(round, prim, r), keep);
+            if (!done) rank[gb + p] = rk_make(round, prim, r);
             if (head[i] && head[i + 1]) {
-                if (!done) st_hint(&SA[gb + r], p, keep);
+                if (!done) SA[gb + r] = p;
             } else {
                 if (PACKED) {
                     stage[outLoc] = ((uint64_t)r << (2 * logS)) | p;
@@ -1335,23 +1334,33 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     if (s_misc[2] >= s_misc[3]) return;
 
     // ---- order the window's own groups [lo, hi) by (group, second, p) ----
-    // The groups are already in place, so only the order INSIDE each group is missing.
-    // Small groups (most of them; all of them in late rounds and on repeat-rich input): every
-    // element counts the smaller keys of its own group and goes straight to its slot - a
-    // few shared-memory loads per element where the merge sort below spends ~200 thread
-    // instructions.  Only when the window holds a group larger than SMALL_GROUP does the
-    // network + merge-path sort run, and then small groups are already in order, so most
-    // of its run pairs are skipped.
+    // The groups are already in place, so only the order INSIDE each group is missing.  If no
+    // group of the window is larger than SMALL_GROUP (late rounds; repeat-rich input, where
+    // nearly every group is a pair) every element counts the smaller keys of its own group
+    // and goes straight to its slot: a few shared-memory loads per element where the merge
+    // sort spends ~200 thread instructions.  Otherwise (text, early rounds) the network +
+    // merge-path sort runs as before; the test costs one load per element (groups are
+    // contiguous: a group is large iff some element's 32nd successor is in the same group).
     constexpr int SMALL_GROUP = 32;
     const int cnt = hi - lo;
     uint64_t k[LITEMS];
     const int j0 = tid * LITEMS;
+    bool large = false;
 #pragma unroll
-    for (int i = 0; i < LITEMS; i++) k[i] = (j0 + i < cnt) ? sk[lphys(lo + j0 + i)] : ~0ull;
-    uint16_t *gsize = (uint16_t *)sh;   // [W] size of the group that starts at an index (the histogram is flushed)
-    {
+    for (int i = 0; i < LITEMS; i++) {
+        const int j = j0 + i;
+        k[i] = (j < cnt) ? sk[lphys(lo + j)] : ~0ull;
+        if (j + SMALL_GROUP < cnt)
+            large = large || (uint32_t)(sk[lphys(lo + j + SMALL_GROUP)] >> (2 * logS)) == (uint32_t)(k[i] >> (2 * logS));
+    }
+    const uint32_t gPrev = (j0 > 0 && j0 <= cnt) ? (uint32_t)(sk[lphys(lo + j0 - 1)] >> (2 * logS)) : 0xffffffffu;
+    const int anyLarge = __syncthreads_or(large ? 1 : 0);   // also: every thread has its elements in registers
+    const int lo0 = lo;   // where the own groups start in the loaded layout
+    hi = cnt;
+    lo = 0;
+    if (!anyLarge) {
+        uint16_t *gsize = (uint16_t *)sh;   // [W] size of the group that starts at an index (the histogram is flushed)
         // start of the group of each of my elements: heads inside my range, else the last head before it
-        const uint32_t gPrev = (j0 > 0 && j0 <= cnt) ? (uint32_t)(sk[lphys(lo + j0 - 1)] >> (2 * logS)) : 0xffffffffu;
         uint32_t headBits = 0;
         uint32_t pg = gPrev;
 #pragma unroll
@@ -1366,7 +1375,7 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) inc = max(inc, __shfl_up_sync(0xffffffffu, inc, o));
         if (lane == 31) swarp[warp].head = inc;
-        __syncthreads();   // also: every thread has its elements in registers
+        __syncthreads();
         uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1);
         if (lane == 0) exc = 0;
         for (int w = 0; w < warp; w++) exc = max(exc, swarp[w].head);
@@ -1384,82 +1393,62 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             if (i & 1) starts[i >> 1] |= start << 16; else starts[i >> 1] = start;
         }
         __syncthreads();
-        // Does the window hold a group larger than SMALL_GROUP?  Then the merge sort runs anyway
-        // and the counting would be extra work (text, early rounds); otherwise counting alone
-        // orders the window (late rounds; repeat-rich input, where every group is a pair).
-        bool large = false;
+        uint32_t dest[LITEMS / 2];
 #pragma unroll
-        for (int i = 0; i < LITEMS; i++)
-            if ((headBits >> i) & 1u) large = large || gsize[j0 + i] > (uint32_t)SMALL_GROUP;
-        const int anyLarge = __syncthreads_or(large ? 1 : 0);
-        if (!anyLarge) {
-            uint32_t dest[LITEMS / 2];
-#pragma unroll
-            for (int i = 0; i < LITEMS; i++) {
-                const int j = j0 + i;
-                uint32_t d = (uint32_t)j;
-                if (j < cnt) {
-                    const uint32_t gs = (starts[i >> 1] >> (16 * (i & 1))) & 0xffffu;
-                    const uint32_t sz = gsize[gs];
-                    if (sz > 1) {
-                        uint32_t r = 0;
-                        for (uint32_t q = 0; q < sz; q++) r += (sk[lphys(lo + (int)(gs + q))] < k[i]) ? 1u : 0u;
-                        d = gs + r;
-                    }
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = j0 + i;
+            uint32_t d = (uint32_t)j;
+            if (j < cnt) {
+                const uint32_t gs = (starts[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+                const uint32_t sz = gsize[gs];
+                if (sz > 1) {
+                    uint32_t r = 0;
+                    for (uint32_t q = 0; q < sz; q++) r += (sk[lphys(lo0 + (int)(gs + q))] < k[i]) ? 1u : 0u;
+                    d = gs + r;
                 }
-                if (i & 1) dest[i >> 1] |= d << 16; else dest[i >> 1] = d;
             }
-            __syncthreads();   // all reads of the old layout are done
-#pragma unroll
-            for (int i = 0; i < LITEMS; i++) sk[lphys((int)((dest[i >> 1] >> (16 * (i & 1))) & 0xffffu))] = k[i];
-        } else {
-            // shifted to the front of the window, padding behind (every element is in registers)
-#pragma unroll
-            for (int i = 0; i < LITEMS; i++) sk[lphys(j0 + i)] = k[i];
+            if (i & 1) dest[i >> 1] |= d << 16; else dest[i >> 1] = d;
         }
+        __syncthreads();   // all reads of the old layout are done
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) sk[lphys((int)((dest[i >> 1] >> (16 * (i & 1))) & 0xffffu))] = k[i];
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < LITEMS; i++) k[i] = sk[lphys(j0 + i)];
-        hi = cnt;
-        lo = 0;
-        if (anyLarge) {
-            // network + merges; a thread whose elements are in order already skips the network
-            bool ordered = true;
-#pragma unroll
-            for (int i = 0; i + 1 < LITEMS; i++) ordered = ordered && (k[i] <= k[i + 1]);
-            if (!ordered) sort_network<LITEMS>(k);
+    } else {
+        // sort the window by (group, second, p): blocked registers, network, merges
+        sort_network<LITEMS>(k);
 #pragma unroll 1
-            for (int width = 1; width < LT; width <<= 1) {
-                __syncthreads();
-#pragma unroll
-                for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
-                __syncthreads();
-                const int pairFirst = tid & ~(2 * width - 1);
-                const int aBeg = pairFirst * LITEMS, bBeg = aBeg + width * LITEMS, bEnd = bBeg + width * LITEMS;
-                if (sk[lphys(bBeg - 1)] > sk[lphys(bBeg)]) {   // otherwise the two runs are already in order
-                    const int diag = (tid - pairFirst) * LITEMS;
-                    const int len = width * LITEMS;
-                    int a = max(0, diag - len), b = min(diag, len);
-                    while (a < b) {
-                        const int m = (a + b) >> 1;
-                        if (sk[lphys(aBeg + m)] <= sk[lphys(bBeg + diag - 1 - m)]) a = m + 1; else b = m;
-                    }
-                    int ai = aBeg + a, bi = bBeg + diag - a;
-                    uint64_t ka = sk[lphys(ai)], kb = sk[lphys(min(bi, W - 1))];
-#pragma unroll
-                    for (int i = 0; i < LITEMS; i++) {
-                        const bool takeB = (bi < bEnd) && (ai >= bBeg || kb < ka);
-                        k[i] = takeB ? kb : ka;
-                        if (takeB) { bi++; kb = sk[lphys(min(bi, W - 1))]; }
-                        else { ai++; ka = sk[lphys(min(ai, W - 1))]; }
-                    }
-                }
-            }
+        for (int width = 1; width < LT; width <<= 1) {
             __syncthreads();
 #pragma unroll
             for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
             __syncthreads();
+            const int pairFirst = tid & ~(2 * width - 1);
+            const int aBeg = pairFirst * LITEMS, bBeg = aBeg + width * LITEMS, bEnd = bBeg + width * LITEMS;
+            if (sk[lphys(bBeg - 1)] > sk[lphys(bBeg)]) {   // otherwise the two runs are already in order
+                const int diag = (tid - pairFirst) * LITEMS;
+                const int len = width * LITEMS;
+                int a = max(0, diag - len), b = min(diag, len);
+                while (a < b) {
+                    const int m = (a + b) >> 1;
+                    if (sk[lphys(aBeg + m)] <= sk[lphys(bBeg + diag - 1 - m)]) a = m + 1; else b = m;
+                }
+                int ai = aBeg + a, bi = bBeg + diag - a;
+                uint64_t ka = sk[lphys(ai)], kb = sk[lphys(min(bi, W - 1))];
+#pragma unroll
+                for (int i = 0; i < LITEMS; i++) {
+                    const bool takeB = (bi < bEnd) && (ai >= bBeg || kb < ka);
+                    k[i] = takeB ? kb : ka;
+                    if (takeB) { bi++; kb = sk[lphys(min(bi, W - 1))]; }
+                    else { ai++; ka = sk[lphys(min(ai, W - 1))]; }
+                }
+            }
         }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) sk[lphys(tid * LITEMS + i)] = k[i];
+        __syncthreads();
     }
 
     // re-rank inside the window: flags, scan, new group ids
@@ -1535,7 +1524,6 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     __syncthreads();   // everyone has read the sorted neighbours: sk can take the survivors
 
     uint32_t curHead = ex.head, curPst = ex.pst, outIdx = ex.keep;
-    const uint64_t keepPol = l2_evict_last();
 #pragma unroll
     for (int i = 0; i < LITEMS; i++) {
         const int j = j0 + i;
@@ -1546,9 +1534,9 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             const uint32_t p = (uint32_t)k[i] & Smask;
             const uint32_t grp = (uint32_t)(k[i] >> (2 * logS));
             const uint32_t r = grp + (curHead - curPst);
-            st_hint(&rank[gb + p], rk_make(round, grp, r), keepPol);
+            rank[gb + p] = rk_make(round, grp, r);
             if (hd && hn) {
-                st_hint(&SA[gb + r], p, keepPol);
+                SA[gb + r] = p;
             } else {
                 sk[outIdx] = ((uint64_t)r << (2 * logS)) | p;
                 outIdx++;
