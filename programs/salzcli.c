@@ -228,10 +228,25 @@ static int pick_devices(int devs[64])
     return n > 64 ? 64 : n;
 }
 
+/* SALZ_CLI_TIMING=1: where the wall time of a compress run goes (stderr). */
+static void phase(const char *what, uint64_t *t)
+{
+    static int on = -1;
+    if (on < 0)
+        on = getenv("SALZ_CLI_TIMING") != NULL;
+    uint64_t now = 0;
+    get_time_ns(&now);
+    if (on && *t)
+        fprintf(stderr, "salz: %-28s %8.1f ms\n", what, (double)(now - *t) / 1e6);
+    *t = now;
+}
+
 static int encoder_acquire(size_t block_len, size_t file_size)
 {
     if (g_enc != NULL)
         return 0;
+    uint64_t t = 0;
+    phase("", &t);
     int devs[64];
     const int ndev = pick_devices(devs);
     if (ndev <= 0) {
@@ -256,6 +271,7 @@ static int encoder_acquire(size_t block_len, size_t file_size)
         say(QUIET_ERR, "Couldn't create CUDA encoder context (no GPU?)");
         return -1;
     }
+    phase("contexts (CUDA init, HBM)", &t);
     g_batch_bytes = blocks * block_len * (size_t)ndev;
     g_out_cap = blocks * (size_t)ndev * ((size_t)salz_encoded_len_max(block_len) + 4);
     /* a file that fits one slot needs one buffer pair only */
@@ -269,6 +285,7 @@ static int encoder_acquire(size_t block_len, size_t file_size)
             return -1;
         }
     }
+    phase("pinned host buffers", &t);
     return 0;
 }
 
@@ -313,7 +330,10 @@ static int do_compress(FILE *in, FILE *out, size_t file_size)
     if (nslot < NSLOT) {
         /* one slot: the file fits it; nothing to overlap */
         struct slot *s = &p.slot[0];
+        uint64_t t = 0;
+        phase("", &t);
         s->got = fread(s->in, 1, p.batch_bytes, in);
+        phase("read", &t);
         if (s->got != p.batch_bytes && ferror(in)) {
             say(QUIET_ERR, "Couldn't read from input stream");
         } else if (s->got == 0 || s->got % block_len == 0 || s->got == p.batch_bytes) {
@@ -321,9 +341,10 @@ static int do_compress(FILE *in, FILE *out, size_t file_size)
         } else if (salz_cuda_multi_encode_stream(g_enc, s->in, s->got, block_len, s->out, g_out_cap, &s->produced, NULL,
                                                  NULL) != 0) {
             say(QUIET_ERR, "Couldn't encode segment");
-        } else if (fwrite(s->out, 1, s->produced, out) != s->produced) {
+        } else if (phase("encode (H2D, kernels, D2H)", &t), fwrite(s->out, 1, s->produced, out) != s->produced) {
             say(QUIET_ERR, "Couldn't write encoded segment to output stream");
         } else {
+            phase("write", &t);
             rc = 0;
         }
         goto done;

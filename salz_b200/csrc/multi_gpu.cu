@@ -256,17 +256,19 @@ extern "C" salz_cuda_multi *salz_cuda_multi_create(const int *devices, int ndev,
     m->stage.assign(ndev, nullptr);
     m->stageCap.assign(ndev, 0);
     for (int i = 0; i < ndev; i++) m->devices.push_back(devices ? devices[i] : i);
+    // One device: nothing to exchange, no communicator (and no dependence on NCCL being
+    // installed); the stream goes straight through that device's context.
     uint8_t id[SALZ_CUDA_UNIQUE_ID_BYTES];
-    bool ok = salz_cuda_comm_unique_id(id) == 0;
+    bool ok = ndev == 1 || salz_cuda_comm_unique_id(id) == 0;
     // ncclCommInitRank blocks until every rank has joined: one thread per device
     std::vector<std::thread> th;
     for (int i = 0; i < ndev && ok; i++)
         th.emplace_back([m, i, &id, max_block_len, max_batch_blocks] {
             m->ctx[i] = salz_cuda_ctx_create(m->devices[i], max_block_len, max_batch_blocks);
-            m->comm[i] = salz_cuda_comm_create(m->devices[i], id, i, m->ndev);
+            if (m->ndev > 1) m->comm[i] = salz_cuda_comm_create(m->devices[i], id, i, m->ndev);
         });
     for (auto &t : th) t.join();
-    for (int i = 0; i < ndev; i++) ok = ok && m->ctx[i] && m->comm[i];
+    for (int i = 0; i < ndev; i++) ok = ok && m->ctx[i] && (ndev == 1 || m->comm[i]);
     if (!ok) {
         fprintf(stderr, "salz_cuda: multi-GPU context creation failed\n");
         salz_cuda_multi_destroy(m);
@@ -306,6 +308,11 @@ extern "C" int salz_cuda_multi_encode_stream(salz_cuda_multi *m, const uint8_t *
         return -1;
     }
     const int G = m->ndev;
+    if (G == 1) {
+        const int r = salz_cuda_encode_stream(m->ctx[0], src, src_len, block_len, dst, dst_cap, dst_len, block_sizes, nblocks_out);
+        if (r != 0) snprintf(m->err, sizeof(m->err), "device %d failed: %s", m->devices[0], salz_cuda_last_error(m->ctx[0]));
+        return r;
+    }
     std::vector<int> rc(G, 0);
     std::vector<size_t> produced(G, 0);
     std::vector<std::vector<uint32_t>> all(G);       // every rank's view of all sizes (must agree)
