@@ -187,13 +187,30 @@ static void *writer_main(void *arg)
 /* Encoder context of the process: created by the first file, reused by the rest. */
 static salz_cuda_multi *g_enc;
 static uint8_t *g_in[NSLOT], *g_out[NSLOT];
+static bool g_pinned[NSLOT];
 static size_t g_batch_bytes, g_out_cap;
+
+/* Slot buffers.  A stream of several slots reuses them many times: page-locked memory, so
+ * that the copies run at full PCIe speed under the kernels.  A file that fits ONE slot is
+ * copied once: pinning its buffers (~1 GB/s) would cost more than it saves, plain memory. */
+static bool slot_alloc(int i, bool pinned)
+{
+    g_pinned[i] = pinned;
+    g_in[i] = pinned ? salz_cuda_host_alloc(g_batch_bytes) : malloc(g_batch_bytes);
+    g_out[i] = pinned ? salz_cuda_host_alloc(g_out_cap) : malloc(g_out_cap);
+    return g_in[i] != NULL && g_out[i] != NULL;
+}
 
 static void encoder_release(void)
 {
     for (int i = 0; i < NSLOT; i++) {
-        salz_cuda_host_free(g_in[i]);
-        salz_cuda_host_free(g_out[i]);
+        if (g_pinned[i]) {
+            salz_cuda_host_free(g_in[i]);
+            salz_cuda_host_free(g_out[i]);
+        } else {
+            free(g_in[i]);
+            free(g_out[i]);
+        }
         g_in[i] = g_out[i] = NULL;
     }
     salz_cuda_multi_destroy(g_enc);
@@ -262,8 +279,8 @@ static int encoder_acquire(size_t block_len, size_t file_size)
     size_t blocks = per_gpu / block_len;
     const size_t file_blocks = file_size / block_len + 1;
     const size_t share = divup(file_blocks, (size_t)ndev);
-    if (blocks > share)
-        blocks = share;
+    if (blocks > share || share <= blocks + blocks / 4)
+        blocks = share;   /* the whole file in one slot (a little over the default batch still is) */
     if (blocks > 65535)
         blocks = 65535;
     g_enc = salz_cuda_multi_create(devs, ndev, block_len, blocks);
@@ -277,15 +294,13 @@ static int encoder_acquire(size_t block_len, size_t file_size)
     /* a file that fits one slot needs one buffer pair only */
     const int nslot = file_size < g_batch_bytes ? 1 : NSLOT;
     for (int i = 0; i < nslot; i++) {
-        g_in[i] = salz_cuda_host_alloc(g_batch_bytes);
-        g_out[i] = salz_cuda_host_alloc(g_out_cap);
-        if (g_in[i] == NULL || g_out[i] == NULL) {
+        if (!slot_alloc(i, nslot > 1)) {
             say(QUIET_ERR, "Couldn't allocate memory: (%zu bytes)", g_batch_bytes + g_out_cap);
             encoder_release();
             return -1;
         }
     }
-    phase("pinned host buffers", &t);
+    phase("host buffers", &t);
     return 0;
 }
 
@@ -298,11 +313,7 @@ static int do_compress(FILE *in, FILE *out, size_t file_size)
     const int want = file_size < g_batch_bytes ? 1 : NSLOT;   /* a later, larger file: all slots */
     for (int i = 0; i < want; i++)
         if (g_in[i] == NULL || g_out[i] == NULL) {
-            if (g_in[i] == NULL)
-                g_in[i] = salz_cuda_host_alloc(g_batch_bytes);
-            if (g_out[i] == NULL)
-                g_out[i] = salz_cuda_host_alloc(g_out_cap);
-            if (g_in[i] == NULL || g_out[i] == NULL) {
+            if (!slot_alloc(i, want > 1)) {
                 say(QUIET_ERR, "Couldn't allocate memory: (%zu bytes)", g_batch_bytes + g_out_cap);
                 return -1;
             }
@@ -603,6 +614,11 @@ int main(int argc, char *argv[])
         int rc = handle_file(argv[i]);
         worst = min(worst, rc);
     }
-    encoder_release();
+    /* Every output file is closed.  Leave without tearing the encoder down: unmapping the
+     * device workspace and the pinned buffers takes longer than compressing a small file,
+     * and the driver reclaims them with the process. */
+    fflush(NULL);
+    if (g_enc != NULL)
+        _exit(worst == 0 ? 0 : 255);
     return worst;
 }

@@ -1342,31 +1342,29 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     // merge-path sort runs as before; the test costs one load per element (groups are
     // contiguous: a group is large iff some element's 32nd successor is in the same group).
     constexpr int SMALL_GROUP = 32;
-    const int cnt = hi - lo;
     uint64_t k[LITEMS];
     const int j0 = tid * LITEMS;
     bool large = false;
 #pragma unroll
     for (int i = 0; i < LITEMS; i++) {
         const int j = j0 + i;
-        k[i] = (j < cnt) ? sk[lphys(lo + j)] : ~0ull;
-        if (j + SMALL_GROUP < cnt)
-            large = large || (uint32_t)(sk[lphys(lo + j + SMALL_GROUP)] >> (2 * logS)) == (uint32_t)(k[i] >> (2 * logS));
+        k[i] = sk[lphys(j)];
+        if (j >= lo && j + SMALL_GROUP < hi)
+            large = large || (uint32_t)(sk[lphys(j + SMALL_GROUP)] >> (2 * logS)) == (uint32_t)(k[i] >> (2 * logS));
     }
-    const uint32_t gPrev = (j0 > 0 && j0 <= cnt) ? (uint32_t)(sk[lphys(lo + j0 - 1)] >> (2 * logS)) : 0xffffffffu;
+    const uint32_t gPrev = (j0 > lo && j0 <= hi) ? (uint32_t)(sk[lphys(j0 - 1)] >> (2 * logS)) : 0xffffffffu;
     const int anyLarge = __syncthreads_or(large ? 1 : 0);   // also: every thread has its elements in registers
-    const int lo0 = lo;   // where the own groups start in the loaded layout
-    hi = cnt;
-    lo = 0;
     if (!anyLarge) {
+        // the own groups stay where they are, [lo, hi); the forwarded elements around them are padding
         uint16_t *gsize = (uint16_t *)sh;   // [W] size of the group that starts at an index (the histogram is flushed)
         // start of the group of each of my elements: heads inside my range, else the last head before it
         uint32_t headBits = 0;
         uint32_t pg = gPrev;
 #pragma unroll
         for (int i = 0; i < LITEMS; i++) {
+            const int j = j0 + i;
             const uint32_t g = (uint32_t)(k[i] >> (2 * logS));
-            if (j0 + i < cnt && (j0 + i == 0 || g != pg)) headBits |= 1u << i;
+            if (j >= lo && j < hi && (j == lo || g != pg)) headBits |= 1u << i;
             pg = g;
         }
         // exclusive max-scan over the threads of (index of my last head + 1)
@@ -1379,17 +1377,17 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
         uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1);
         if (lane == 0) exc = 0;
         for (int w = 0; w < warp; w++) exc = max(exc, swarp[w].head);
-        // sizes: a head closes the group before it; the end of the window closes the last one
-        uint32_t start = exc ? exc - 1u : 0u;
+        // sizes: a head closes the group before it; the end of the own range closes the last one
+        uint32_t start = exc ? exc - 1u : (uint32_t)lo;
         uint32_t starts[LITEMS / 2];   // two 16-bit group starts per register
 #pragma unroll
         for (int i = 0; i < LITEMS; i++) {
             const int j = j0 + i;
             if ((headBits >> i) & 1u) {
-                if (j > 0) gsize[start] = (uint16_t)(j - (int)start);
+                if (j > lo) gsize[start] = (uint16_t)(j - (int)start);
                 start = (uint32_t)j;
             }
-            if (j == cnt - 1) gsize[start] = (uint16_t)(cnt - (int)start);
+            if (j == hi - 1) gsize[start] = (uint16_t)(hi - (int)start);
             if (i & 1) starts[i >> 1] |= start << 16; else starts[i >> 1] = start;
         }
         __syncthreads();
@@ -1398,25 +1396,28 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
         for (int i = 0; i < LITEMS; i++) {
             const int j = j0 + i;
             uint32_t d = (uint32_t)j;
-            if (j < cnt) {
+            if (j >= lo && j < hi) {
                 const uint32_t gs = (starts[i >> 1] >> (16 * (i & 1))) & 0xffffu;
                 const uint32_t sz = gsize[gs];
                 if (sz > 1) {
                     uint32_t r = 0;
-                    for (uint32_t q = 0; q < sz; q++) r += (sk[lphys(lo0 + (int)(gs + q))] < k[i]) ? 1u : 0u;
+                    for (uint32_t q = 0; q < sz; q++) r += (sk[lphys((int)(gs + q))] < k[i]) ? 1u : 0u;
                     d = gs + r;
                 }
             }
             if (i & 1) dest[i >> 1] |= d << 16; else dest[i >> 1] = d;
         }
-        __syncthreads();   // all reads of the old layout are done
+        __syncthreads();   // all reads of the old order are done
 #pragma unroll
         for (int i = 0; i < LITEMS; i++) sk[lphys((int)((dest[i >> 1] >> (16 * (i & 1))) & 0xffffu))] = k[i];
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < LITEMS; i++) k[i] = sk[lphys(j0 + i)];
     } else {
-        // sort the window by (group, second, p): blocked registers, network, merges
+        // sort the window by (group, second, p): blocked registers, network, merges; the padding
+        // sorts to the end, so the own groups end up in [0, hi - lo)
+        hi -= lo;
+        lo = 0;
         sort_network<LITEMS>(k);
 #pragma unroll 1
         for (int width = 1; width < LT; width <<= 1) {

@@ -14,6 +14,6 @@ d.tofile('/dev/shm/salzcli/a.bin')
 PY
 make -s -C lib
 for i in 1 2; do
-  /usr/bin/env time -f "wall %e s" env SALZ_CLI_TIMING=1 programs/salz -k -f -5 /dev/shm/salzcli/a.bin 2>&1 | tee -a gpurun_out/cli.txt
+  ( time env SALZ_CLI_TIMING=1 programs/salz -k -f -5 /dev/shm/salzcli/a.bin ) 2>&1 | tee -a gpurun_out/cli.txt
 done
 rm -rf /dev/shm/salzcli
