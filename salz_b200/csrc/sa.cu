@@ -1224,6 +1224,7 @@ struct HK3 { uint32_t head, pst, keep; };  // head/pst: window index + 1 of the 
 #ifndef SALZ_LCTAS
 #define SALZ_LCTAS 3
 #endif
+template <bool COUNT>
 __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__restrict__ keysIn, ListView lv,
                                               const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ h0,
                                               int logS, uint32_t round, int passes, uint64_t *__restrict__ rank,
@@ -1353,7 +1354,10 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             large = large || (uint32_t)(sk[lphys(j + SMALL_GROUP)] >> (2 * logS)) == (uint32_t)(k[i] >> (2 * logS));
     }
     const uint32_t gPrev = (j0 > lo && j0 <= hi) ? (uint32_t)(sk[lphys(j0 - 1)] >> (2 * logS)) : 0xffffffffu;
-    const int anyLarge = __syncthreads_or(large ? 1 : 0);   // also: every thread has its elements in registers
+    // COUNT = false (the host's choice for the first rounds, where nearly every window of a text
+    // holds a large group): the counting path is not even compiled in - its presence costs the
+    // merge path 10 % through register allocation (measured: 25.7 -> 26.3 ms of SA per step)
+    const int anyLarge = COUNT ? __syncthreads_or(large ? 1 : 0) : 1;   // also: every thread has its elements in registers
     if (!anyLarge) {
         // the own groups stay where they are, [lo, hi); the forwarded elements around them are padding
         uint16_t *gsize = (uint16_t *)sh;   // [W] size of the group that starts at an index (the histogram is flushed)
@@ -1793,8 +1797,12 @@ int sa_build_local(SortCtx &s, int &rounds)
         CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
         CK(cudaMemsetAsync(ws.listCnt[vNext], 0, (size_t)bd.B * 4, s.st));
         CK(cudaMemsetAsync(ws.listCnt[2], 0, (size_t)bd.B * 4, s.st));
-        k_local<<<tiles, LT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, round, passes, ws.rank, ws.SA,
-                                        ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.listCnt[2], ws.hist);
+        if (round >= (uint32_t)ws.localCountRound)
+            k_local<true><<<tiles, LT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, round, passes, ws.rank, ws.SA,
+                                                  ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.listCnt[2], ws.hist);
+        else
+            k_local<false><<<tiles, LT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, round, passes, ws.rank, ws.SA,
+                                                   ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.listCnt[2], ws.hist);
         s.lc.launches += 1;
         s.algBytes += (uint64_t)count * 32;
         if (dbg(s, "k_local")) return -1;
