@@ -1069,9 +1069,12 @@ __device__ __forceinline__ HK rr_lookback(ulonglong2 *state, uint32_t tile, uint
     return acc;
 }
 
-template <bool PACKED, bool ROUND0>
+// gShift: bit position of the group id in a packed bag element (2 logS, or 64 - logS when the
+// block capacity is above 2^21).  BAGOUT (pairs input only): survivors leave as packed bag
+// elements (group << gShift | p) instead of pairs.
+template <bool PACKED, bool ROUND0, bool BAGOUT>
 __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
-                                                     ListView lv, int logS, uint32_t round,
+                                                     ListView lv, int logS, int gShift, uint32_t round,
                                                      uint64_t *__restrict__ rank, uint32_t *__restrict__ SA,
                                                      uint64_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut,
                                                      const uint32_t *__restrict__ cntBefore,
@@ -1167,7 +1170,9 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
                 if (!done) SA[gb + r] = p;
             } else {
                 if (PACKED) {
-                    stage[outLoc] = ((uint64_t)r << (2 * logS)) | p;
+                    stage[outLoc] = ((uint64_t)r << gShift) | p;
+                } else if (BAGOUT) {
+                    keysOut[outBase + outLoc] = ((uint64_t)r << gShift) | p;
                 } else {
                     keysOut[outBase + outLoc] = (uint64_t)r << logS;
                     valsOut[outBase + outLoc] = p;
@@ -1224,16 +1229,22 @@ struct HK3 { uint32_t head, pst, keep; };  // head/pst: window index + 1 of the 
 #ifndef SALZ_LCTAS
 #define SALZ_LCTAS 3
 #endif
-template <bool COUNT>
+// WIDE (block capacity above 2^21: group, second and p no longer fit one u64): bag elements are
+// (group << gShift | p) with gShift = 64 - logS; inside the window the key carries the group's
+// index in the window (at most 4096: 12 bits) instead of its id, the ids wait in gid[]; groups
+// that cross the window are forwarded as pairs (key = group << logS | second, value = p).
+template <bool COUNT, bool WIDE>
 __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__restrict__ keysIn, ListView lv,
                                               const uint32_t *__restrict__ blkN, const uint32_t *__restrict__ h0,
-                                              int logS, uint32_t round, int passes, uint64_t *__restrict__ rank,
+                                              int logS, int gShift, uint32_t round, int passes, uint64_t *__restrict__ rank,
                                               uint32_t *__restrict__ SA, uint64_t *__restrict__ outS,
                                               uint32_t *__restrict__ cntS, uint64_t *__restrict__ outL,
-                                              uint32_t *__restrict__ cntL, uint32_t *__restrict__ hist)
+                                              uint32_t *__restrict__ outLv, uint32_t *__restrict__ cntL,
+                                              uint32_t *__restrict__ hist)
 {
     constexpr int W = LTILE, NW = LT / 32;
     __shared__ __align__(16) uint64_t sk[W + W / LITEMS + 2];
+    extern __shared__ uint32_t gid[];        // WIDE: [W] group id of every window position (dynamic: beyond the 48 KB static limit)
     __shared__ uint32_t sh[MAXP * 256];
     __shared__ HK3 swarp[NW + 1];
     __shared__ uint32_t s_misc[8];
@@ -1268,30 +1279,37 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             if (e[i] != ~0ull) {
                 const uint32_t p = (uint32_t)e[i] & Smask;
                 const uint32_t sec = (p + h < n) ? rk_read(rv[i], round) + 1u : 0u;
-                key = ((e[i] >> (2 * logS)) << (2 * logS)) | ((uint64_t)sec << logS) | p;
+                if (WIDE) {
+                    key = ((uint64_t)sec << logS) | p;             // the window index of the group is added below
+                    gid[j] = (uint32_t)(e[i] >> gShift);
+                } else {
+                    key = ((e[i] >> (2 * logS)) << (2 * logS)) | ((uint64_t)sec << logS) | p;
+                }
             }
             sk[lphys(j)] = key;
         }
     }
+    // group id of window position j (before the forwarded elements are blanked)
+    auto grpAt = [&](int j) -> uint32_t { return WIDE ? gid[j] : (uint32_t)(sk[lphys(j)] >> (2 * logS)); };
     if (tid == 0) {
         const uint32_t segCnt = lv.cnt[tl.b];
         uint32_t prevG = 0xffffffffu, nextG = 0xffffffffu;
-        if (tl.lt > 0) prevG = (uint32_t)(keysIn[tl.first - 1] >> (2 * logS));
-        if (tl.lt * (uint32_t)W + tl.valid < segCnt) nextG = (uint32_t)(keysIn[tl.first + valid] >> (2 * logS));
+        if (tl.lt > 0) prevG = (uint32_t)(keysIn[tl.first - 1] >> gShift);
+        if (tl.lt * (uint32_t)W + tl.valid < segCnt) nextG = (uint32_t)(keysIn[tl.first + valid] >> gShift);
         s_misc[0] = prevG;
         s_misc[1] = nextG;
     }
     __syncthreads();
     // crossing groups: a prefix [0, lo) and a suffix [hi, valid) of the window
     if (warp == 0) {
-        const uint32_t gFirst = (uint32_t)(sk[lphys(0)] >> (2 * logS));
-        const uint32_t gLast = (uint32_t)(sk[lphys(valid - 1)] >> (2 * logS));
+        const uint32_t gFirst = grpAt(0);
+        const uint32_t gLast = grpAt(valid - 1);
         int lo = 0, hi = valid;
         if (s_misc[0] == gFirst) {  // first j with group > gFirst
             int a = 0, b = valid;
             while (a < b) {
                 const int m = (a + b) >> 1;
-                if ((uint32_t)(sk[lphys(m)] >> (2 * logS)) == gFirst) a = m + 1; else b = m;
+                if (grpAt(m) == gFirst) a = m + 1; else b = m;
             }
             lo = a;
         }
@@ -1299,7 +1317,7 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             int a = 0, b = valid;
             while (a < b) {
                 const int m = (a + b) >> 1;
-                if ((uint32_t)(sk[lphys(m)] >> (2 * logS)) != gLast) a = m + 1; else b = m;
+                if (grpAt(m) != gLast) a = m + 1; else b = m;
             }
             hi = a;
         }
@@ -1321,8 +1339,15 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
         for (int idx = tid; idx < nCross; idx += LT) {
             const int j = (idx < lo) ? idx : hi + (idx - lo);
             const uint64_t key = sk[lphys(j)];
-            outL[gb + lbase + idx] = key;
-            const uint64_t kf = key >> logS;
+            uint64_t kf;
+            if (WIDE) {   // pairs: key = (group, second), value = p
+                kf = ((uint64_t)gid[j] << logS) | (key >> logS);
+                outL[gb + lbase + idx] = kf;
+                outLv[gb + lbase + idx] = (uint32_t)key & Smask;
+            } else {
+                outL[gb + lbase + idx] = key;
+                kf = key >> logS;
+            }
             for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
         }
         __syncthreads();
@@ -1333,6 +1358,37 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
         __syncthreads();
     }
     if (s_misc[2] >= s_misc[3]) return;
+    const int lo0 = lo;   // gid[] stays indexed by the window position an element was loaded at
+
+    if (WIDE) {
+        // the own groups get their index in the window as the group field of the key: heads of
+        // my 16 consecutive positions, exclusive count over the threads before me
+        const int jb = tid * LITEMS;
+        uint32_t hb = 0;
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = jb + i;
+            if (j >= lo && j < hi && (j == lo || gid[j] != gid[j - 1])) hb |= 1u << i;
+        }
+        uint32_t inc = __popc(hb);
+        const uint32_t mine = inc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) swarp[warp].keep = inc;
+        __syncthreads();
+        uint32_t before = inc - mine;
+        for (int w = 0; w < warp; w++) before += swarp[w].keep;
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = jb + i;
+            if ((hb >> i) & 1u) before++;
+            if (j >= lo && j < hi) sk[lphys(j)] |= (uint64_t)(before - 1u) << (2 * logS);
+        }
+        __syncthreads();
+    }
 
     // ---- order the window's own groups [lo, hi) by (group, second, p) ----
     // The groups are already in place, so only the order INSIDE each group is missing.  If no
@@ -1528,6 +1584,14 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     const uint32_t sbase = s_misc[5];
     __syncthreads();   // everyone has read the sorted neighbours: sk can take the survivors
 
+    uint32_t sgid[WIDE ? LITEMS : 1];
+    if (WIDE) {
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = j0 + i;
+            sgid[i] = (j >= lo && j < hi) ? gid[j + (lo == 0 ? lo0 : 0)] : 0u;
+        }
+    }
     uint32_t curHead = ex.head, curPst = ex.pst, outIdx = ex.keep;
 #pragma unroll
     for (int i = 0; i < LITEMS; i++) {
@@ -1537,13 +1601,14 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             if (hd) curHead = j + 1;
             if ((pstBits >> i) & 1u) curPst = j + 1;
             const uint32_t p = (uint32_t)k[i] & Smask;
-            const uint32_t grp = (uint32_t)(k[i] >> (2 * logS));
+            // WIDE: sorting kept every group where it was (shifted to the front by the merge path)
+            const uint32_t grp = WIDE ? sgid[i] : (uint32_t)(k[i] >> (2 * logS));
             const uint32_t r = grp + (curHead - curPst);
             rank[gb + p] = rk_make(round, grp, r);
             if (hd && hn) {
                 SA[gb + r] = p;
             } else {
-                sk[outIdx] = ((uint64_t)r << (2 * logS)) | p;
+                sk[outIdx] = ((uint64_t)r << gShift) | p;
                 outIdx++;
             }
         }
@@ -1575,6 +1640,7 @@ struct SortCtx {
     float *msSort;
     cudaEvent_t evA, evB;
     uint64_t algBytes;
+    int gShift;   // bit position of the group id in a packed bag element
 };
 
 // SALZ_DEBUG_SYNC=1: synchronise after every stage and name the one that failed.
@@ -1623,8 +1689,9 @@ int fetch_counters(SortCtx &s)
 // in keys[src]; the other buffer is keys[dst].  Returns the buffer holding the result.
 template <bool PACKED>
 int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, int shift0, int src, int dst,
-               uint32_t skipMask = 0)
+               uint32_t skipMask = 0, int *vbuf = nullptr)
 {
+    int vs = vbuf ? *vbuf : (src & 1), vd = vs ^ 1;   // value buffers of the pairs format
     Workspace &ws = s.ws;
     int done = 0;   // passes actually run (skipMask: passes that are the identity for every block)
     if (s.msSort) CK(cudaEventRecord(s.evA, s.st));
@@ -1672,20 +1739,22 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
             done++;
             CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
             if (s.matchAny)
-                k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst], ws.vals[dst & 1],
+                k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[vs], ws.keys[dst], ws.vals[vd],
                                                                   view(ws, v), tiles, shift0 + 8 * ps, ps, ws.digitBase,
                                                                   ws.tileState);
             else
-                k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[src & 1], ws.keys[dst],
-                                                                   ws.vals[dst & 1], view(ws, v), tiles, shift0 + 8 * ps, ps,
+                k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[vs], ws.keys[dst],
+                                                                   ws.vals[vd], view(ws, v), tiles, shift0 + 8 * ps, ps,
                                                                    ws.digitBase, ws.tileState);
             s.lc.launches += 1;
             s.lc.sort_launches += 1;
             s.lc.sort_elems += count;
             s.lc.sort_bytes += (uint64_t)count * (PACKED ? 16 : 24);
             std::swap(src, dst);
+            std::swap(vs, vd);
         }
     }
+    if (vbuf) *vbuf = vs;
     if (s.msSort) CK(cudaEventRecord(s.evB, s.st));
     CK(cudaGetLastError());
     s.algBytes += (uint64_t)count * (PACKED ? 16 : 24) * done;
@@ -1706,18 +1775,20 @@ int add_sort_time(SortCtx &s)
 // Re-rank the sorted list (view v, in keys[src]): finished suffixes go to SA, the
 // survivors are appended to keys[dst] behind cntBefore[b] elements per block and
 // counted into listCnt[vNext].
-template <bool PACKED, bool ROUND0>
+template <bool PACKED, bool ROUND0, bool BAGOUT = false>
 int rerank(SortCtx &s, int v, uint32_t count, uint32_t tiles, int src, int dst, uint32_t round,
-           const uint32_t *cntBefore, int vNext)
+           const uint32_t *cntBefore, int vNext, int vsrc = -1)
 {
     Workspace &ws = s.ws;
     const int logS = s.bd.logS;
     const ListView lv = view(ws, v);
+    if (vsrc < 0) vsrc = src & 1;
     // single pass: tile prefixes by look-back (the scatter passes' tile state is free by now)
     ulonglong2 *look = (ulonglong2 *)ws.tileState;
     CK(cudaMemsetAsync(look, 0, (size_t)tiles * sizeof(ulonglong2), s.st));
-    k_rerank_apply<PACKED, ROUND0><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[src & 1], lv, logS, round, ws.rank, ws.SA, ws.keys[dst],
-                                                           ws.vals[dst & 1], cntBefore, ws.listCnt[vNext], look);
+    k_rerank_apply<PACKED, ROUND0, BAGOUT><<<tiles, TT, 0, s.st>>>(ws.keys[src], ws.vals[vsrc], lv, logS, s.gShift, round, ws.rank,
+                                                                   ws.SA, ws.keys[dst], ws.vals[dst & 1], cntBefore,
+                                                                   ws.listCnt[vNext], look);
     s.lc.launches += 1;
     s.algBytes += (uint64_t)count * (PACKED ? 20 : 28);
     CK(cudaGetLastError());
@@ -1742,7 +1813,7 @@ int alphabet(SortCtx &s, int fieldBits)
 // Round 0 on list view 2 (every suffix of every block), result re-ranked into
 // keys[dstBuf] / listCnt[vNext].  Returns through count/tiles the sizes used.
 template <bool PACKED>
-int round0(SortCtx &s, int passes, int shift0, int vNext, int *bufOut)
+int round0(SortCtx &s, int fieldBits, int passes, int shift0, int vNext, int *bufOut)
 {
     Workspace &ws = s.ws;
     const BatchDesc &bd = s.bd;
@@ -1750,7 +1821,7 @@ int round0(SortCtx &s, int passes, int shift0, int vNext, int *bufOut)
     const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
     uint32_t tiles = 0;
     for (int b = 0; b < bd.B; b++) tiles += (ws.h_blkN[b] - 8 + TILE - 1) / TILE;
-    if (alphabet(s, 2 * logS)) return -1;
+    if (alphabet(s, fieldBits)) return -1;
     k_first_counts<<<(bd.B + 255) / 256, 256, 0, s.st>>>(ws.blkN, bd.B, ws.listCnt[2]);
     tilemap(s, 2, TILE, 0);
     CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
@@ -1768,17 +1839,24 @@ int round0(SortCtx &s, int passes, int shift0, int vNext, int *bufOut)
     return 0;
 }
 
-// PACKED batches: round 0, then rounds of k_local (+ the global path for the
-// groups that cross windows) until no suffix is left in the bag.
+// Packed bag: round 0, then rounds of k_local (+ the global path for the groups that cross
+// windows) until no suffix is left in the bag.  Block capacities up to 2^21 keep (group,
+// second, p) in one u64 everywhere.  Above that (WIDE, CLI levels 7-9) the round-0 key takes
+// the 64 - logS bits beside p, the bag holds (group << (64 - logS) | p), k_local works with
+// window-local group indices, and only the groups that cross windows travel as pairs
+// (u64 key + u32 value) through the global radix path.
 int sa_build_local(SortCtx &s, int &rounds)
 {
     Workspace &ws = s.ws;
     const BatchDesc &bd = s.bd;
     const int logS = bd.logS;
-    const int passes = (2 * logS + 7) / 8;
+    const bool wide = 3 * logS > 64;
+    const int fieldBits = wide ? 64 - logS : 2 * logS;      // round-0 key
+    const int passes0 = (fieldBits + 7) / 8;
+    const int passes = (2 * logS + 7) / 8;                   // (group, second) key of the global path
     const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
     int bufS = 0;
-    if (round0<true>(s, passes, logS, 0, &bufS)) return -1;
+    if (round0<true>(s, fieldBits, passes0, logS, 0, &bufS)) return -1;
     int vS = 0;
     tilemap(s, vS, LTILE, 0);
     if (fetch_counters(s)) return -1;
@@ -1797,12 +1875,17 @@ int sa_build_local(SortCtx &s, int &rounds)
         CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
         CK(cudaMemsetAsync(ws.listCnt[vNext], 0, (size_t)bd.B * 4, s.st));
         CK(cudaMemsetAsync(ws.listCnt[2], 0, (size_t)bd.B * 4, s.st));
-        if (round >= (uint32_t)ws.localCountRound)
-            k_local<true><<<tiles, LT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, round, passes, ws.rank, ws.SA,
-                                                  ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.listCnt[2], ws.hist);
-        else
-            k_local<false><<<tiles, LT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, round, passes, ws.rank, ws.SA,
-                                                   ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.listCnt[2], ws.hist);
+        const bool cnt = round >= (uint32_t)ws.localCountRound;
+#define SALZ_LOCAL_ARGS ws.keys[bufS], view(ws, vS), ws.blkN, ws.h0, logS, s.gShift, round, passes, ws.rank, ws.SA, \
+                        ws.keys[bufOut], ws.listCnt[vNext], ws.keys[bufL], ws.vals[0], ws.listCnt[2], ws.hist
+        if (wide) {
+            if (cnt) k_local<true, true><<<tiles, LT, LTILE * 4, s.st>>>(SALZ_LOCAL_ARGS);
+            else k_local<false, true><<<tiles, LT, LTILE * 4, s.st>>>(SALZ_LOCAL_ARGS);
+        } else {
+            if (cnt) k_local<true, false><<<tiles, LT, 0, s.st>>>(SALZ_LOCAL_ARGS);
+            else k_local<false, false><<<tiles, LT, 0, s.st>>>(SALZ_LOCAL_ARGS);
+        }
+#undef SALZ_LOCAL_ARGS
         s.lc.launches += 1;
         s.algBytes += (uint64_t)count * 32;
         if (dbg(s, "k_local")) return -1;
@@ -1816,10 +1899,16 @@ int sa_build_local(SortCtx &s, int &rounds)
         const uint32_t countL = ws.h_counters[2], tilesL = ws.h_counters[3];
         if (countL > 0) {
             const uint32_t skip = ws.h_counters[12] & ((1u << passes) - 1u);
-            const int res = radix_sort<true>(s, 2, countL, tilesL, passes, logS, bufL, bufS, skip);
+            int vres = 0;   // pairs: the forwarded values start in vals[0]
+            const int res = wide ? radix_sort<false>(s, 2, countL, tilesL, passes, 0, bufL, bufS, skip, &vres)
+                                 : radix_sort<true>(s, 2, countL, tilesL, passes, logS, bufL, bufS, skip);
             if (res < 0) return -1;
             CK(cudaMemcpyAsync(ws.cntSnap, ws.listCnt[vNext], (size_t)bd.B * 4, cudaMemcpyDeviceToDevice, s.st));
-            if (rerank<true, false>(s, 2, countL, tilesL, res, bufOut, round, ws.cntSnap, vNext)) return -1;
+            if (wide) {
+                if (rerank<false, false, true>(s, 2, countL, tilesL, res, bufOut, round, ws.cntSnap, vNext, vres)) return -1;
+            } else {
+                if (rerank<true, false>(s, 2, countL, tilesL, res, bufOut, round, ws.cntSnap, vNext)) return -1;
+            }
             tilemap(s, vNext, LTILE, 0);
             if (fetch_counters(s)) return -1;
             if (add_sort_time(s)) return -1;
@@ -1844,7 +1933,7 @@ int sa_build_pairs(SortCtx &s, int &rounds)
     const int passes = (2 * logS + 7) / 8;
     const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
     int cur = 0;
-    if (round0<false>(s, passes, 0, 0, &cur)) return -1;
+    if (round0<false>(s, 2 * logS, passes, 0, 0, &cur)) return -1;
     int v = 0;
     tilemap(s, v, TILE, 0);
     if (fetch_counters(s)) return -1;
@@ -1893,6 +1982,8 @@ int sa_init_device()
     CK(cudaFuncSetAttribute(k_scatter<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PACKED));
     CK(cudaFuncSetAttribute(k_scatter<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
     CK(cudaFuncSetAttribute(k_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM_PAIRS));
+    CK(cudaFuncSetAttribute(k_local<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LTILE * 4));
+    CK(cudaFuncSetAttribute(k_local<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LTILE * 4));
     CK(cudaFuncSetAttribute(k_scatter_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     return 0;
@@ -1902,14 +1993,14 @@ int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st, 
              uint64_t &algBytes, int &rounds, float *msSort)
 {
     if (bd.M == 0) return 0;
-    SortCtx s = {ws, bd, st, lc, sortMode == 0, msSort, nullptr, nullptr, 0};
+    const bool packed = 3 * bd.logS <= 64;
+    SortCtx s = {ws, bd, st, lc, sortMode == 0, msSort, nullptr, nullptr, 0, packed ? 2 * bd.logS : 64 - bd.logS};
     if (msSort) {
         CK(cudaEventCreate(&s.evA));
         CK(cudaEventCreate(&s.evB));
         *msSort = 0.f;
     }
-    const bool packed = 3 * bd.logS <= 64;
-    int rc = packed ? sa_build_local(s, rounds) : sa_build_pairs(s, rounds);
+    int rc = (packed || ws.wideLocal) ? sa_build_local(s, rounds) : sa_build_pairs(s, rounds);
     algBytes += s.algBytes;
     if (msSort) {
         cudaEventDestroy(s.evA);

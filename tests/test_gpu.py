@@ -263,6 +263,32 @@ def test_level9_block(orc):
         e.close()
 
 
+def test_wide_blocks_all_stages(orc):
+    """Block capacity above 2^21 (CLI levels 7-9): group, second key and position no longer fit
+    one u64, so the bag holds (group, p), k_local works with window-local group indices and the
+    groups that cross windows travel as pairs.  Same stages, same bytes - on inputs small enough
+    to compare every stage, and on one 4 MiB block of each kind."""
+    e = salz_b200.SalzCuda(0, 1 << 22, 2)
+    try:
+        cases = synth.small_cases(5)[:15] + [
+            ("eng300k", synth.english_like(300000, seed=3)),
+            ("dna300k", synth.dna_like(300000, seed=4, block=300000)),
+            ("a200k", np.full(200000, 0x61, np.uint8)),
+            ("period5", np.resize(np.frombuffer(b"abcab", np.uint8), 150001)),
+            ("rand100k", synth.uniform_random(100000, seed=6)),
+        ]
+        for name, data in cases:
+            _check_stages(e, orc, "wide/" + name, data)
+        for name, data in (("eng4M", synth.english_like(1 << 22, seed=7)), ("dna4M", synth.dna_like(1 << 22, seed=8, block=1 << 22)),
+                           ("a4M", np.full(1 << 22, 0x62, np.uint8))):
+            assert e.encode(data) == orc.encode(data), name
+        texts = [c[1] for c in cases[15:]]
+        for t, sa in zip(texts, e.suffix_arrays(texts)):
+            assert np.array_equal(sa, orc.suffix_array(t))
+    finally:
+        e.close()
+
+
 def _host_lib():
     subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "lib")], check=True)
     lib = C.CDLL(os.path.join(ROOT, "lib", "libsalz.so"))
