@@ -11,27 +11,33 @@
 // known; it is always ordered by group, and a group id is the SA slot of the
 // group's first member.  One round:
 //
-//   k_build    key = (group id, 1 + group id of suffix p+h, 0 past the end)
-//   k_scatter  stable LSD radix passes over the key bits (8 bits per pass):
+//   key        (group id, 1 + group id of suffix p+h, 0 past the end), built where the
+//              element is read (k_local)
+//   k_scatter* stable LSD radix passes over the key bits (8 bits per pass):
 //              per-warp shared-memory digit counters, ranks from warp-wide
 //              peer masks (shared-memory atomicOr, or match_any), decoupled
 //              look-back over per-tile digit counts, keys staged through
-//              shared memory in digit order and written back as coalesced runs
+//              shared memory in digit order and written back as coalesced runs;
+//              k_scatter_tma: tiles arrive by cp.async.bulk on an mbarrier ring, issued
+//              by a dedicated producer warp
 //   k_rerank_* adjacent-key compare + scan: new group ids; suffixes whose
 //              group became a singleton are written to SA and dropped
 //
-// Element formats.  PACKED (block capacity S <= 2^21): one u64 per element,
-//   (group:logS | second:logS | p:logS); a pass moves 16 B per element.
-// Otherwise: u64 key (group | second) + u32 value p; 24 B per element.
+// Element formats.  The bag (suffixes not yet placed) is always ONE u64 per element:
+//   block capacity S <= 2^21:  (group:logS | second:logS | p:logS), the same layout on the
+//                              global radix path; a pass moves 16 B per element
+//   S > 2^21 (CLI levels 7-9): (group << (64 - logS) | p); the three fields meet only inside a
+//                              k_local window, where the group is replaced by its index in the
+//                              window; groups that cross windows travel as pairs (u64 key =
+//                              group << logS | second, u32 value = p; 24 B per element per pass)
 //
-// PACKED batches take a cheaper route in the doubling rounds (k_local): the
-// list is a bag of contiguous groups, and a group that lies inside one
-// 4096-element window is sorted by its second key in shared memory (register
-// sorting network + merge-path merges that skip already ordered runs),
-// re-ranked and compacted by the same CTA - one read and one write of the
-// element instead of five scatter passes.  Only groups that cross a window
-// boundary (large groups, and the odd unlucky small one) are forwarded to the
-// global radix path above; their survivors are appended to the bag again.
+// In the doubling rounds (k_local) the list is a bag of contiguous groups, and a group
+// that lies inside one 4096-element window is ordered by its second key in shared memory
+// (counting inside small groups; register sorting network + merge-path merges that skip
+// already ordered runs otherwise), re-ranked and compacted by the same CTA - one read and
+// one write of the element instead of five scatter passes.  Only groups that cross a window
+// boundary (large groups, and the odd unlucky small one) are forwarded to the global radix
+// path above; their survivors are appended to the bag again.
 //
 // Round 0 sorts by the first h0 characters after remapping the block's bytes to
 // dense codes of ceil(log2(sigma)) bits (k_alphabet), so 2 logS key bits cover
@@ -325,41 +331,6 @@ __global__ void __launch_bounds__(TT) k_init(const uint8_t *__restrict__ T, size
                 keys[tl.first + idx] = kf;
                 vals[tl.first + idx] = p;
             }
-            for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
-        }
-    }
-    __syncthreads();
-    hist_flush(sh, passes, hist, tl.b);
-}
-
-// Doubling round of the global path: the list holds (group, -, p); second = 1 +
-// group id of suffix p+h, 0 past the end; h = h0[b] << (round - 1).
-template <bool PACKED>
-__global__ void __launch_bounds__(TT) k_build(const uint64_t *__restrict__ rank, const uint32_t *__restrict__ blkN,
-                                              ListView lv, int logS, const uint32_t *__restrict__ h0, uint32_t round,
-                                              int passes, uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals,
-                                              uint32_t *__restrict__ hist)
-{
-    __shared__ uint32_t sh[MAXP * 256];
-    for (int i = threadIdx.x; i < passes * 256; i += TT) sh[i] = 0;
-    __syncthreads();
-    const TileLoc tl = locate(lv, blockIdx.x);
-    const uint32_t n = blkN[tl.b] - 8;
-    const uint32_t h = h0[tl.b] << (round - 1);
-    const uint32_t Smask = (1u << logS) - 1;
-    const uint64_t *rk = rank + ((size_t)tl.b << logS);
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t idx = threadIdx.x + i * TT;
-        if (idx < tl.valid) {
-            const uint64_t e = keys[tl.first + idx];
-            uint32_t p, prim;
-            if (PACKED) { p = (uint32_t)e & Smask; prim = (uint32_t)(e >> (2 * logS)); }
-            else { p = vals[tl.first + idx]; prim = (uint32_t)(e >> logS); }
-            uint32_t sec = 0;
-            if (p + h < n) sec = rk_read(rk[p + h], round) + 1;
-            const uint64_t kf = ((uint64_t)prim << logS) | sec;
-            keys[tl.first + idx] = PACKED ? ((kf << logS) | p) : kf;
             for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((uint32_t)(kf >> (8 * ps)) & 255u)], 1u);
         }
     }
@@ -1924,52 +1895,6 @@ int sa_build_local(SortCtx &s, int &rounds)
     return 0;
 }
 
-// Block capacity above 2^21 (pairs format): every round re-sorts the whole list.
-int sa_build_pairs(SortCtx &s, int &rounds)
-{
-    Workspace &ws = s.ws;
-    const BatchDesc &bd = s.bd;
-    const int logS = bd.logS;
-    const int passes = (2 * logS + 7) / 8;
-    const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;
-    int cur = 0;
-    if (round0<false>(s, 2 * logS, passes, 0, 0, &cur)) return -1;
-    int v = 0;
-    tilemap(s, v, TILE, 0);
-    if (fetch_counters(s)) return -1;
-    if (add_sort_time(s)) return -1;
-    uint32_t count = ws.h_counters[0], tiles = ws.h_counters[1];
-    rounds = 0;
-    uint32_t round = 1;
-    while (count > 0) {
-        if (round > 27) {
-            fprintf(stderr, "salz_cuda: prefix doubling failed to converge (round %u)\n", round);
-            return -1;
-        }
-        CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
-        k_build<false><<<tiles, TT, 0, s.st>>>(ws.rank, ws.blkN, view(ws, v), logS, ws.h0, round, passes, ws.keys[cur],
-                                               ws.vals[cur], ws.hist);
-        k_scan_hist<<<dim3(passes, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase, nullptr, nullptr);
-        s.lc.launches += 2;
-        s.algBytes += (uint64_t)count * 28;
-        const int res = radix_sort<false>(s, v, count, tiles, passes, 0, cur, cur ^ 1);
-        if (res < 0) return -1;
-        CK(cudaMemsetAsync(ws.listCnt[v ^ 1], 0, (size_t)bd.B * 4, s.st));
-        if (rerank<false, false>(s, v, count, tiles, res, res ^ 1, round, nullptr, v ^ 1)) return -1;
-        v ^= 1;
-        cur = res ^ 1;
-        tilemap(s, v, TILE, 0);
-        if (fetch_counters(s)) return -1;
-        if (add_sort_time(s)) return -1;
-        count = ws.h_counters[0];
-        tiles = ws.h_counters[1];
-        round++;
-        rounds++;
-    }
-    CK(cudaGetLastError());
-    return 0;
-}
-
 }  // namespace
 
 int sa_tile_elems() { return TILE < LTILE ? TILE : LTILE; }
@@ -2000,7 +1925,7 @@ int sa_build(Workspace &ws, const BatchDesc &bd, int sortMode, cudaStream_t st, 
         CK(cudaEventCreate(&s.evB));
         *msSort = 0.f;
     }
-    int rc = (packed || ws.wideLocal) ? sa_build_local(s, rounds) : sa_build_pairs(s, rounds);
+    int rc = sa_build_local(s, rounds);
     algBytes += s.algBytes;
     if (msSort) {
         cudaEventDestroy(s.evA);
