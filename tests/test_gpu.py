@@ -263,6 +263,29 @@ def test_level9_block(orc):
         e.close()
 
 
+def test_repeated_runs_are_deterministic(orc):
+    """The sort leans on relaxed loads/stores for two decoupled look-backs, on ranks read and
+    written in one launch (stamps) and on self-cleaning shared-memory masks; compute-sanitizer's
+    racecheck is closed on this GPU pool (profiles/r02_sanitizer_closed.txt).  A race there shows
+    up as run-to-run differences under different schedules: the same stream, many times, three
+    batch shapes (different tile interleavings), both ranking modes - always the reference's bytes."""
+    bl = 1 << 16
+    data = np.concatenate([synth.english_like(37 * bl, seed=51), synth.dna_like(20 * bl, seed=52, block=bl),
+                           np.full(6 * bl, 0x41, np.uint8), synth.uniform_random(3 * bl + 999, seed=53)])
+    want = b""
+    for off in range(0, len(data), bl):
+        blk = orc.encode(data[off: off + bl])
+        want += len(blk).to_bytes(4, "little") + blk
+    for bmax in (67, 23, 5):
+        e = salz_b200.SalzCuda(0, bl, bmax)
+        try:
+            for rep in range(6):
+                e.set_sort_mode(rep & 1)
+                assert e.encode_stream(data, bl)[0] == want, (bmax, rep)
+        finally:
+            e.close()
+
+
 def test_wide_blocks_all_stages(orc):
     """Block capacity above 2^21 (CLI levels 7-9): group, second key and position no longer fit
     one u64, so the bag holds (group, p), k_local works with window-local group indices and the
