@@ -1822,7 +1822,8 @@ int sa_build_local(SortCtx &s, int &rounds)
     const BatchDesc &bd = s.bd;
     const int logS = bd.logS;
     const bool wide = 3 * logS > 64;
-    const int fieldBits = wide ? 64 - logS : 2 * logS;      // round-0 key
+    int fieldBits = wide ? 64 - logS : 2 * logS;            // round-0 key
+    if (ws.round0Bits > 0 && ws.round0Bits < fieldBits) fieldBits = ws.round0Bits;
     const int passes0 = (fieldBits + 7) / 8;
     const int passes = (2 * logS + 7) / 8;                   // (group, second) key of the global path
     const size_t histBytes = (size_t)bd.B * MAXP * 256 * 4;

@@ -10,7 +10,9 @@ echo "ncu0 exit $?"
 ncu --set full --clock-control none -k regex:'k_scatter|k_local|k_parse|k_choose|k_rerank_apply|k_ansv_tile|k_plcp_irreducible|k_plcp_apply|k_init|k_emit_tokens' -c 48 -f -o /tmp/prof_main $CMD > gpurun_out/ncu1.log 2>&1
 echo "ncu1 exit $?"
 ncu -i /tmp/prof_main.ncu-rep --page raw --csv > gpurun_out/main_raw.csv 2>/dev/null
-ncu --set full --clock-control none --import-source on -k regex:'k_parse|k_ansv_tile|k_plcp_irreducible' -c 3 -f -o /tmp/prof_src $CMD > gpurun_out/ncu2.log 2>&1
-echo "ncu2 exit $?"
-ncu -i /tmp/prof_src.ncu-rep --page source --csv > gpurun_out/src.csv 2>/dev/null
+for K in k_scatter_tma k_local k_ansv_tile; do
+  ncu --set full --clock-control none --import-source on -k regex:$K -c 1 -f -o /tmp/prof_src_$K $CMD > gpurun_out/ncu2_$K.log 2>&1
+  echo "ncu2 $K exit $?"
+  ncu -i /tmp/prof_src_$K.ncu-rep --page source --csv > gpurun_out/src_$K.csv 2>/dev/null
+done
 ls -la gpurun_out/
