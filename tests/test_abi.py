@@ -50,6 +50,19 @@ def test_no_cpu_fallback():
     assert lib.salz_encode_safe(src, 100, dst, C.byref(n)) == -1
 
 
+def test_multi_gpu_entry_points_fail_loudly_without_gpu():
+    """salz_cuda_multi_create / salz_cuda_comm_create: no device -> NULL -> the mirror raises
+    (no CPU stand-in for the sharded path either); the block ranges need no device."""
+    from salz_b200 import api
+    assert api.block_range(8193, 0, 8) == (0, 1025) and api.block_range(8193, 7, 8) == (7169, 8193)
+    if not _no_gpu():
+        pytest.skip("GPU present")
+    with pytest.raises(salz_b200.SalzCudaError):
+        salz_b200.SalzCudaMulti(ndev=0)
+    with pytest.raises(salz_b200.SalzCudaError):
+        salz_b200.ShardComm(0, bytes(128), 0, 1)
+
+
 def test_host_decoder_and_vnibble(port, ref):
     lib = C.CDLL(os.path.join(ROOT, "lib", "libsalz.so"))
     lib.salz_decode_safe.argtypes = [C.c_char_p, C.c_size_t, C.c_char_p, C.POINTER(C.c_size_t)]
