@@ -38,7 +38,6 @@ constexpr int APAD = AL + 1;        // padded segment stride in shared memory
 constexpr int32_t AINF = 0x7fffffff;
 constexpr uint32_t LINK_PM = 0x80;  // element is a prefix minimum; low 7 bits = next prefix minimum
 constexpr uint32_t LINK_NONE = 0x7f;
-constexpr uint64_t FAR_NONE = ~0ull;   // unused slot of a tile's chunk of the far list
 
 // far item: slot (30 bits) | side (1 bit, 1 = right) | partial LCP minimum (31 bits)
 __device__ __forceinline__ uint64_t far_item(uint32_t slot, uint32_t right, int32_t acc)
@@ -58,11 +57,6 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     __shared__ int32_t segMin[AT], segLcp[AT];
     __shared__ int32_t preV[AT], preL[AT], sufV[AT], sufL[AT];  // minima over the segments before / after
     __shared__ uint8_t segLen[AT];
-    // far items of the tile go into a chunk of the global list reserved with ONE atomic at the
-    // start of the CTA (a global atomic per item sat in the threads' serial chains: 6.6 % of the
-    // stall samples); what is left of the chunk is filled with FAR_NONE, which k_ansv_far skips
-    constexpr uint32_t FARCHUNK = 64;
-    __shared__ uint32_t sfarCnt, sfarBase;
 
     const int tid = threadIdx.x;
     const uint32_t tilesPerBlock = 1u << (logS - 12);
@@ -83,14 +77,10 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     // kept in L2 (evict_last) until the other pieces arrive; SA and LCP stream through
     const uint64_t keep = l2_evict_last(), stream = l2_evict_first();
 
-    if (tid == 0) {
-        sfarCnt = 0;
-        sfarBase = atomicAdd(farCount, FARCHUNK);
-    }
-    // tile load, sixteen slots per thread at a time: the loads of a batch are all in flight before
+    // tile load, eight slots per thread at a time: the loads of a batch are all in flight before
     // the first of them is used (one load per loop iteration exposed the DRAM latency 32 times:
     // 23 % of this kernel's stall samples sat on the first use, profiles/r01_v15_ncu_stalls.txt)
-    constexpr int LDB = 16;
+    constexpr int LDB = 8;
 #pragma unroll 1
     for (int base = 0; base < AL; base += LDB) {
         uint32_t a[LDB];
@@ -185,12 +175,7 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         }
     }
     __syncthreads();
-    auto push_far = [&](uint64_t item) {
-        const uint32_t k = atomicAdd(&sfarCnt, 1u);
-        if (k < FARCHUNK) farItems[sfarBase + k] = item;
-        else farItems[atomicAdd(farCount, 1u)] = item;   // chunk full: one more slot
-    };
-    if (len > 0) {
+    if (len == 0) return;
 
     const bool firstTile = (tb == 0), lastTile = (t0 + ATS >= n);
     // ---- level 2, left: my prefix minima look for their PSV in earlier segments ----
@@ -218,7 +203,7 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         } else if (firstTile) {
             st_hint(&cd[2 * v], make_int2(v + 1, 0), keep);       // no PSV: offs = p - (-1), len 0 (ref lib/salz.c:546-560)
         } else {
-            push_far(far_item((uint32_t)gb + t0 + tid * AL + i, 0, acc));
+            farItems[atomicAdd(farCount, 1u)] = far_item((uint32_t)gb + t0 + tid * AL + i, 0, acc);
         }
         const uint32_t nx = w & 0x7fu;
         i = (nx == LINK_NONE) ? -1 : (int)nx;
@@ -254,15 +239,12 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
                 else st_hint(&cd[2 * v + 1], make_int2(v + 1, 0), keep);
             } else {
                 if (havePsv) st_hint(&cd[2 * v], ps, keep);
-                push_far(far_item((uint32_t)gb + t0 + tid * AL + e, 1, acc));
+                farItems[atomicAdd(farCount, 1u)] = far_item((uint32_t)gb + t0 + tid * AL + e, 1, acc);
             }
             accR = min(accR, sm[sb + e]);
             e = (w & LINK_PM) ? -1 : (int)(w & 0x7fu);
         }
     }
-    }   // len > 0
-    __syncthreads();
-    for (uint32_t k = min(sfarCnt, FARCHUNK) + tid; k < FARCHUNK; k += AT) farItems[sfarBase + k] = FAR_NONE;
 }
 
 // ---------------------------------------------------------------------------
@@ -279,7 +261,6 @@ __global__ void __launch_bounds__(256) k_ansv_far(Pyr py, const uint32_t *__rest
     const uint32_t count = *farCount;
     for (uint32_t it = blockIdx.x * 256 + threadIdx.x; it < count; it += gridDim.x * 256) {
         const uint64_t item = farItems[it];
-        if (item == FAR_NONE) continue;
         const uint32_t slot = (uint32_t)(item >> 32);
         const bool right = (item >> 31) & 1;
         int32_t m = (int32_t)(item & 0x7fffffffu);
