@@ -149,6 +149,31 @@ void salz_cuda_set_parse_segments(salz_cuda_ctx *ctx, int k);
  * so that events the caller records on that stream bracket the work. */
 void salz_cuda_set_stream(salz_cuda_ctx *ctx, void *stream);
 
+/* ---- no-allocation entry point --------------------------------------------------
+ *
+ * No counterpart in the reference; added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).
+ *
+ * PLCP and LCP of ONE text from its suffix array (the arrays salz_cuda_debug_stages
+ * returns as plcp / lcp), all buffers the caller's DEVICE memory on `device`:
+ *   d_text[n] the text, d_sa[n] its suffix array, d_lcp[n] out (LCP[0] = 0,
+ *   LCP[r] = lcp(SA[r-1], SA[r])), d_plcp[n] out or NULL.
+ * The work is queued on `stream` (a cudaStream_t as void *, NULL = the default
+ * stream); the call does not synchronise.  It calls no cudaMalloc / cudaFree and no
+ * allocating library routine: its scratch (text copy, inverse suffix array, PLCP
+ * values) is a static device array of SALZ_CUDA_NOALLOC_MAX_N positions, ~3.3 MiB
+ * that every GPU which loads the library holds until exit.  n above that limit is
+ * rejected (-2, message on stderr); other errors return -1; n == 0 only performs the
+ * once-per-device set-up (do that before a graph capture starts).  All calls share
+ * the one array, which keeps the last call's contents (what must start at zero is
+ * cleared on `stream` at every call): calls that overlap on the same GPU - from
+ * different streams or threads - race; serialise them. */
+#define SALZ_CUDA_NOALLOC_MAX_N ((size_t)1 << 18)
+int salz_cuda_lcp_noalloc(int device, const uint8_t *d_text, size_t n,
+                          const int32_t *d_sa, int32_t *d_plcp, int32_t *d_lcp,
+                          void *stream);
+
 /* ---- multi-GPU: blocks sharded over the GPUs of one box -------------
  *
  * Replaces nothing in the reference (it is single-threaded); the unit that is

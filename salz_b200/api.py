@@ -24,7 +24,10 @@ EXPORTS = [
     "salz_cuda_comm_rank", "salz_cuda_comm_world", "salz_cuda_comm_gathers", "salz_cuda_comm_allgather_sizes",
     "salz_cuda_multi_create", "salz_cuda_multi_destroy", "salz_cuda_multi_devices", "salz_cuda_multi_ctx",
     "salz_cuda_multi_last_error", "salz_cuda_multi_encode_stream",
+    # no-allocation entry point (csrc/lcp.cu)
+    "salz_cuda_lcp_noalloc",
 ]
+NOALLOC_MAX_N = 1 << 18
 UNIQUE_ID_BYTES = 128
 
 
@@ -77,6 +80,7 @@ def load_library():
     L.salz_cuda_host_alloc.argtypes = [C.c_size_t]
     L.salz_cuda_host_free.argtypes = [C.c_void_p]
     u64p = C.POINTER(C.c_uint64)
+    L.salz_cuda_lcp_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.salz_cuda_block_range.restype = None
     L.salz_cuda_block_range.argtypes = [C.c_size_t, C.c_int, C.c_int, szp, szp]
     L.salz_cuda_comm_unique_id.argtypes = [u8p]

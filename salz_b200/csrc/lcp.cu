@@ -295,3 +295,121 @@ int pyramid_upper_build(Workspace &ws, const BatchDesc &bd, cudaStream_t st, Lau
     }
     return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
+
+// ---- no-allocation entry point -------------------------------------------------------------
+// salz_cuda_lcp_noalloc (include/salz_cuda.h): PLCP / LCP of one text from its suffix array with
+// the kernels above, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// Its scratch - a zero-padded copy of the text, the inverse
+// suffix array, the PLCP values, the tile maxima, the block descriptor - lives in the file-scope
+// array below: SALZ_CUDA_NOALLOC_MAX_N positions at most, ~3.3 MiB that every GPU which loads
+// the library holds until exit.  In host code the array's NAME is a host-side stand-in, not a
+// device address; the address comes from cudaGetSymbolAddress, once per device with that device
+// current.  All calls share the array and it keeps the last call's contents: what must start at
+// zero is cleared on the caller's stream at every call, and calls that overlap on one GPU race.
+#include "../../include/salz_cuda.h"
+
+#include <mutex>
+
+namespace {
+
+constexpr size_t NA_MAXN = SALZ_CUDA_NOALLOC_MAX_N;          // positions; also the largest S
+static_assert((NA_MAXN & (NA_MAXN - 1)) == 0 && NA_MAXN >= 4096, "power of two, at least one ANSV tile");
+constexpr size_t NA_OFF_TEXT = 0;                              // u8  [S + 256], zero behind the text
+constexpr size_t NA_OFF_RANK = NA_OFF_TEXT + NA_MAXN + 256;    // u64 [S]  inverse suffix array
+constexpr size_t NA_OFF_V = NA_OFF_RANK + 8 * NA_MAXN;         // i32 [S]  V, then PLCP
+constexpr size_t NA_OFF_TMAX = NA_OFF_V + 4 * NA_MAXN;         // i32 [S / LT] tile maxima (start at zero)
+constexpr size_t NA_OFF_BLKN = NA_OFF_TMAX + 4 * (NA_MAXN / LT);   // u32 [1] N = n + 8
+constexpr size_t NA_BYTES = NA_OFF_BLKN + 256;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// rank[SA[r]] = r (the low 24 bits are what the PLCP kernels read); thread 0 leaves the block
+// descriptor.  A suffix-array entry outside [0, n) is skipped and counted.
+__global__ void __launch_bounds__(256) k_noalloc_isa(const int32_t *__restrict__ SA, uint32_t n, uint64_t *__restrict__ rank,
+                                                     uint32_t *__restrict__ blkN)
+{
+    const uint32_t r = blockIdx.x * 256 + threadIdx.x;
+    if (r == 0) blkN[0] = n + 8;
+    if (r < n) {
+        const uint32_t p = (uint32_t)SA[r];
+        if (p < n) rank[p] = r;
+    }
+}
+
+std::mutex g_noalloc_mu;
+unsigned char *g_noalloc_ptr[64];   // per device: device address of g_noalloc_scratch
+
+}  // namespace
+
+extern "C" int salz_cuda_lcp_noalloc(int device, const uint8_t *d_text, size_t n, const int32_t *d_sa, int32_t *d_plcp,
+                                     int32_t *d_lcp, void *stream)
+{
+    if (device < 0 || device >= 64) {
+        fprintf(stderr, "salz_cuda_lcp_noalloc: device %d out of range\n", device);
+        return -1;
+    }
+    if (n > NA_MAXN) {
+        fprintf(stderr, "salz_cuda_lcp_noalloc: %zu positions exceed the static scratch (SALZ_CUDA_NOALLOC_MAX_N = %zu); "
+                        "use a salz_cuda_ctx for larger texts\n", n, NA_MAXN);
+        return -2;
+    }
+    if (n > 0 && (!d_text || !d_sa || !d_lcp)) {
+        fprintf(stderr, "salz_cuda_lcp_noalloc: NULL text, suffix array or LCP buffer\n");
+        return -1;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) {
+        fprintf(stderr, "salz_cuda_lcp_noalloc: no CUDA device %d; there is no CPU fallback\n", device);
+        return -1;
+    }
+    unsigned char *base;
+    {
+        // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            void *p = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) {
+                fprintf(stderr, "salz_cuda_lcp_noalloc: cudaGetSymbolAddress: %s\n", cudaGetErrorString(e));
+                return -1;
+            }
+            g_noalloc_ptr[device] = (unsigned char *)p;
+        }
+        base = g_noalloc_ptr[device];
+    }
+    if (n == 0) return 0;   // set-up only (e.g. before a graph capture starts)
+
+    cudaStream_t st = (cudaStream_t)stream;
+    int logS = 12;
+    while (((size_t)1 << logS) < n) logS++;
+    const size_t S = (size_t)1 << logS;
+    uint8_t *T = base + NA_OFF_TEXT;
+    uint64_t *rank = (uint64_t *)(base + NA_OFF_RANK);
+    int32_t *V = (int32_t *)(base + NA_OFF_V);
+    int32_t *tileMax = (int32_t *)(base + NA_OFF_TMAX);
+    uint32_t *blkN = (uint32_t *)(base + NA_OFF_BLKN);
+    const uint32_t tiles = (uint32_t)(S / LT);
+
+    // the array keeps the last call's contents: the text padding and the tile maxima must start at
+    // zero; so does the inverse suffix array, so that a malformed d_sa (not a permutation) cannot
+    // leave a stale slot behind that indexes past d_sa
+    cudaError_t e = cudaMemsetAsync(T, 0, S + 256, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(rank, 0, S * sizeof(uint64_t), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(tileMax, 0, (size_t)tiles * sizeof(int32_t), st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(T, d_text, n, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) {
+        fprintf(stderr, "salz_cuda_lcp_noalloc: %s\n", cudaGetErrorString(e));
+        return -1;
+    }
+    k_noalloc_isa<<<(uint32_t)((n + 255) / 256), 256, 0, st>>>(d_sa, (uint32_t)n, rank, blkN);
+    k_plcp_irreducible<<<tiles * (LT / (IT * PI)), IT, 0, st>>>(T, S, blkN, rank, (const uint32_t *)d_sa, logS, V, tileMax);
+    k_plcp_scan_tiles<<<1, 256, 0, st>>>(tileMax, tiles);
+    k_plcp_apply<<<tiles, LT, 0, st>>>(blkN, rank, logS, tileMax, V, d_lcp);
+    e = cudaGetLastError();
+    if (e == cudaSuccess && d_plcp) e = cudaMemcpyAsync(d_plcp, V, n * sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) {
+        fprintf(stderr, "salz_cuda_lcp_noalloc: %s\n", cudaGetErrorString(e));
+        return -1;
+    }
+    return 0;
+}
