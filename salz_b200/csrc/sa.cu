@@ -712,6 +712,62 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
             key[i] = (idx < tl.valid) ? skeys[idx] : ~0ull;
         }
+        uint32_t lr[ITEMS / 2];       // RANK2 >= 2: warp-local ranks of a pair of keys, 16 bits each
+        if (RANK2 >= 2) {
+            // ONE peer-mask step per key: the rank of a key among the keys of its warp with the
+            // same digit (running per-warp counter + lower peers) stays in a register, and the
+            // counters end up as the warp's digit histogram.  No separate counting atomics, and
+            // after the scan a key needs two independent loads and a store.
+#pragma unroll
+            for (int j = 0; j < ITEMS / 2; j++) {
+                const uint32_t d0 = (uint32_t)(key[2 * j] >> shift) & 255u, d1 = (uint32_t)(key[2 * j + 1] >> shift) & 255u;
+                const uint32_t p2 = d0 | (d1 << 8);
+                dd[j] = p2;
+                uint32_t r0, r1;
+                if (__reduce_and_sync(0xffffffffu, p2) == __reduce_or_sync(0xffffffffu, p2)) {
+                    const uint32_t c0 = mycnt[d0];
+                    const uint32_t c1 = mycnt[d1];
+                    r0 = c0 + lane;
+                    r1 = ((d0 == d1) ? c0 + 32 : c1) + lane;
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (d0 == d1) mycnt[d0] = c0 + 64;
+                        else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
+                    }
+                } else if (RANK2 == 3) {   // both keys of the pair in one step, two mask arrays
+                    atomicOr(&myA[d0], laneBit);
+                    atomicOr(&myB[d1], laneBit);
+                    __syncwarp();
+                    const uint32_t m0 = myA[d0], m1 = myB[d1];
+                    const uint32_t x = myA[d1];     // first keys with my second key's digit
+                    const uint32_t y = myB[d0];     // second keys with my first key's digit
+                    const uint32_t c0 = mycnt[d0], c1 = mycnt[d1];
+                    __syncwarp();
+                    r0 = c0 + __popc(m0 & lt_mask);
+                    r1 = c1 + __popc(x) + __popc(m1 & lt_mask);
+                    if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0) + __popc(y); }
+                    if (lane == __ffs(m1) - 1) { myB[d1] = 0; if (x == 0) mycnt[d1] = c1 + __popc(m1); }
+                } else {
+                    atomicOr(&myA[d0], laneBit);
+                    __syncwarp();
+                    const uint32_t m0 = myA[d0];
+                    const uint32_t c0 = mycnt[d0];
+                    __syncwarp();
+                    r0 = c0 + __popc(m0 & lt_mask);
+                    if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0); }
+                    __syncwarp();
+                    atomicOr(&myA[d1], laneBit);
+                    __syncwarp();
+                    const uint32_t m1 = myA[d1];
+                    const uint32_t c1 = mycnt[d1];
+                    __syncwarp();
+                    r1 = c1 + __popc(m1 & lt_mask);
+                    if (lane == __ffs(m1) - 1) { myA[d1] = 0; mycnt[d1] = c1 + __popc(m1); }
+                }
+                lr[j] = r0 | (r1 << 16);
+                __syncwarp();   // leaders' stores before the next step's atomics
+            }
+        } else {
         // early counts: published before the ranking so that successors find aggregates
 #pragma unroll
         for (int j = 0; j < ITEMS / 2; j++) {
@@ -728,6 +784,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                 atomicAdd(&mycnt[d0], 1u);
                 atomicAdd(&mycnt[d1], 1u);
             }
+        }
         }
         consumer_sync();   // counts complete; every key of the slot is in registers
 
@@ -763,6 +820,16 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
         consumer_sync();
 
+        if (RANK2 >= 2) {
+            // the counters now hold the exclusive prefix over the warps before mine
+#pragma unroll
+            for (int j = 0; j < ITEMS / 2; j++) {
+                const uint32_t d0 = dd[j] & 255u, d1 = dd[j] >> 8;
+                skeys[dstart[d0] + mycnt[d0] + (lr[j] & 0xffffu)] = key[2 * j];
+                skeys[dstart[d1] + mycnt[d1] + (lr[j] >> 16)] = key[2 * j + 1];
+            }
+            __syncwarp();
+        } else
         // ranking: peers of a lane = lanes of the warp holding the same digit
 #pragma unroll
         for (int j = 0; j < ITEMS / 2; j++) {
@@ -1656,6 +1723,19 @@ int fetch_counters(SortCtx &s)
     return 0;
 }
 
+// SALZ_SCATTER: 1 = counts first, then ranking; 2 = the same with two keys per ranking step;
+// 3 = one ranking pass, warp-local ranks kept in registers; 4 = the same, two keys per step
+void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, uint64_t *b, const ListView &lv,
+                        const PassPlan &pp, const uint32_t *digitBase, uint32_t *tileState)
+{
+    switch (mode) {
+    case 2: k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
+    case 3: k_scatter_tma<2><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
+    case 4: k_scatter_tma<3><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
+    default: k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
+    }
+}
+
 // `passes` LSD passes over list view `v` (count elements in `tiles` tiles), starting
 // in keys[src]; the other buffer is keys[dst].  Returns the buffer holding the result.
 template <bool PACKED>
@@ -1677,10 +1757,7 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
             CK(cudaMemsetAsync(ws.passDone, 0, (size_t)s.bd.B * MAXP * 4, s.st));
             k_sched<<<(tickets + 255) / 256, 256, 0, s.st>>>(ws.tileBase[v], ws.tileDesc[v], tiles, passes, ws.sortGroup, ws.sched);
             const PassPlan pp = {ws.sched, tickets, 0, shift0, ws.passDone};
-            if (ws.scatterMode == 2)
-                k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
-            else
-                k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+            launch_scatter_tma(ws.scatterMode, grid, s.st, ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
             s.lc.launches += 2;
             s.lc.sort_launches += 1;
             done = passes;
@@ -1690,10 +1767,7 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
                 if ((skipMask >> ps) & 1u) continue;
                 if (done) CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
                 const PassPlan pp = {nullptr, tiles, ps, shift0 + 8 * ps, nullptr};
-                if (ws.scatterMode == 2)
-                    k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
-                else
-                    k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, s.st>>>(ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
+                launch_scatter_tma(ws.scatterMode, grid, s.st, ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
                 s.lc.launches += 1;
                 s.lc.sort_launches += 1;
                 done++;
@@ -1912,6 +1986,8 @@ int sa_init_device()
     CK(cudaFuncSetAttribute(k_local<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LTILE * 4));
     CK(cudaFuncSetAttribute(k_scatter_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
+    CK(cudaFuncSetAttribute(k_scatter_tma<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
+    CK(cudaFuncSetAttribute(k_scatter_tma<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     return 0;
 }
 
