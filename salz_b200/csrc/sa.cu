@@ -619,6 +619,25 @@ __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
 // barrier among the consumer warps only (the producer warp never joins it)
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(TT) : "memory"); }
 
+// -DSALZ_SCATTER_PROF: thread 0 of every CTA accumulates the cycles between the marks of a tile;
+// CTAs 0 and 150 print their sums at exit (A/B builds only: profiles/r02_scatter_phases.txt).
+#ifdef SALZ_SCATTER_PROF
+#define PROF_DECL unsigned long long prof_[12] = {0}, prof_t_ = 0; uint32_t prof_tiles_ = 0;
+#define PROF_START() do { if (tid == 0) prof_t_ = clock64(); } while (0)
+#define PROF_MARK(i) do { if (tid == 0) { const unsigned long long n_ = clock64(); prof_[i] += n_ - prof_t_; prof_t_ = n_; } } while (0)
+#define PROF_TILE() do { if (tid == 0) prof_tiles_++; } while (0)
+#define PROF_PRINT() do { if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == 150) && prof_tiles_) \
+    printf("scatter prof cta %u mode %d tiles %u: wait %llu count %llu bar1 %llu reduce %llu bar23 %llu rank %llu lookback %llu bar4 %llu write %llu bar5 %llu (cycles per tile)\n", \
+           blockIdx.x, RANK2, prof_tiles_, prof_[0] / prof_tiles_, prof_[1] / prof_tiles_, prof_[2] / prof_tiles_, prof_[3] / prof_tiles_, prof_[4] / prof_tiles_, \
+           prof_[5] / prof_tiles_, prof_[6] / prof_tiles_, prof_[7] / prof_tiles_, prof_[8] / prof_tiles_, prof_[9] / prof_tiles_); } while (0)
+#else
+#define PROF_DECL
+#define PROF_START() do {} while (0)
+#define PROF_MARK(i) do {} while (0)
+#define PROF_TILE() do {} while (0)
+#define PROF_PRINT() do {} while (0)
+#endif
+
 template <int RANK2>
 __global__ void __launch_bounds__(TTHREADS, SALZ_TCTAS)
 k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const uint32_t *__restrict__ digitBase,
@@ -691,11 +710,15 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t laneBit = 1u << lane;
 
+    PROF_DECL
     for (uint32_t it = 0;; it++) {
         const int k = it % TSLOTS;
+        PROF_START();
         mbar_wait(&full[k], (it / TSLOTS) & 1);
         const uint32_t *sd = sdesc + 8 * k;
         if (sd[0] >= pp.numTickets) break;
+        PROF_MARK(0);
+        PROF_TILE();
         const uint32_t tile = sd[1], ps = sd[2];
         TileLoc tl;
         tl.b = sd[3]; tl.lt = sd[4]; tl.first = sd[5]; tl.valid = sd[6];
@@ -724,7 +747,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                 const uint32_t p2 = d0 | (d1 << 8);
                 dd[j] = p2;
                 uint32_t r0, r1;
-                if (__reduce_and_sync(0xffffffffu, p2) == __reduce_or_sync(0xffffffffu, p2)) {
+                if (RANK2 != 4 && __reduce_and_sync(0xffffffffu, p2) == __reduce_or_sync(0xffffffffu, p2)) {
                     const uint32_t c0 = mycnt[d0];
                     const uint32_t c1 = mycnt[d1];
                     r0 = c0 + lane;
@@ -734,6 +757,26 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                         if (d0 == d1) mycnt[d0] = c0 + 64;
                         else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
                     }
+                } else if (RANK2 == 4) {
+                    // peer masks from 8 votes on the digit bits: no shared memory, no dependency
+                    // between the keys; what is left of the chain is the running counter
+                    uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu;
+#pragma unroll
+                    for (int b = 0; b < 8; b++) {
+                        const bool b0 = (d0 >> b) & 1u, b1 = (d1 >> b) & 1u;
+                        const uint32_t v0 = __ballot_sync(0xffffffffu, b0), v1 = __ballot_sync(0xffffffffu, b1);
+                        m0 &= b0 ? v0 : ~v0;
+                        m1 &= b1 ? v1 : ~v1;
+                    }
+                    const uint32_t c0 = mycnt[d0];
+                    __syncwarp();
+                    r0 = c0 + __popc(m0 & lt_mask);
+                    if (lane == __ffs(m0) - 1) mycnt[d0] = c0 + __popc(m0);
+                    __syncwarp();
+                    const uint32_t c1 = mycnt[d1];
+                    __syncwarp();
+                    r1 = c1 + __popc(m1 & lt_mask);
+                    if (lane == __ffs(m1) - 1) mycnt[d1] = c1 + __popc(m1);
                 } else if (RANK2 == 3) {   // both keys of the pair in one step, two mask arrays
                     atomicOr(&myA[d0], laneBit);
                     atomicOr(&myB[d1], laneBit);
@@ -786,7 +829,9 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             }
         }
         }
+        PROF_MARK(1);
         consumer_sync();   // counts complete; every key of the slot is in registers
+        PROF_MARK(2);
 
         uint32_t total = 0, ex = 0;
         if (tid < 256) {
@@ -810,6 +855,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             if (lane == 31) scratch[warp] = inc;
             ex = inc - total;
         }
+        PROF_MARK(3);
         consumer_sync();
         if (tid < 256) {
             uint32_t wb = 0;
@@ -819,6 +865,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             dstart[tid] = ex;
         }
         consumer_sync();
+        PROF_MARK(4);
 
         if (RANK2 >= 2) {
             // the counters now hold the exclusive prefix over the warps before mine
@@ -881,6 +928,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
         // the warp's counters are its own again: cleared for the next tile
         for (int i = lane; i < 256; i += 32) mycnt[i] = 0;
+        PROF_MARK(5);
 
         if (tid < 256) {
             uint32_t prev = 0;
@@ -906,7 +954,9 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             }
             gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pp.pass0 + ps) * 256 + tid] + prev - ex;
         }
+        PROF_MARK(6);
         consumer_sync();
+        PROF_MARK(7);
 
         for (uint32_t j = tid; j < tl.valid; j += TT) {
             const uint64_t kk = skeys[j];
@@ -914,7 +964,9 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
         // this thread's generic-proxy accesses to the slot precede the bulk copy that refills it
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        PROF_MARK(8);
         consumer_sync();   // the slot is free, the tile is written
+        PROF_MARK(9);
         if (tid == 0) {
             mbar_arrive(&empty[k]);
             if (pp.passDone) {
@@ -923,6 +975,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             }
         }
     }
+    PROF_PRINT();
 }
 
 // Schedule of a multi-pass launch: group-major (all passes over `group` consecutive blocks,
@@ -1724,7 +1777,8 @@ int fetch_counters(SortCtx &s)
 }
 
 // SALZ_SCATTER: 1 = counts first, then ranking; 2 = the same with two keys per ranking step;
-// 3 = one ranking pass, warp-local ranks kept in registers; 4 = the same, two keys per step
+// 3 = one ranking pass, warp-local ranks kept in registers; 4 = the same, two keys per step;
+// 5 = one ranking pass with peer masks from 8 votes on the digit bits (no mask arrays)
 void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, uint64_t *b, const ListView &lv,
                         const PassPlan &pp, const uint32_t *digitBase, uint32_t *tileState)
 {
@@ -1732,6 +1786,7 @@ void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, u
     case 2: k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     case 3: k_scatter_tma<2><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     case 4: k_scatter_tma<3><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
+    case 5: k_scatter_tma<4><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     default: k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     }
 }
@@ -1988,6 +2043,7 @@ int sa_init_device()
     CK(cudaFuncSetAttribute(k_scatter_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
+    CK(cudaFuncSetAttribute(k_scatter_tma<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     return 0;
 }
 
