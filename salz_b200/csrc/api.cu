@@ -101,6 +101,8 @@ extern "C" salz_cuda_ctx *salz_cuda_ctx_create(int device, size_t max_block_len,
     ws.parseSegments = ps ? atoi(ps) : 0;
     const char *scm = getenv("SALZ_SCATTER"), *sgr = getenv("SALZ_SORT_GROUP");
     ws.scatterMode = scm ? atoi(scm) : 1;   // measured: 0 10.89 ms of sort per step, 1 10.12, 2 10.58
+    const char *bro = getenv("SALZ_BAG_REORDER");
+    ws.bagReorder = bro ? atoi(bro) : 3;
     const char *r0b = getenv("SALZ_R0_BITS");
     ws.round0Bits = r0b ? atoi(r0b) : 0;
     const char *lcr = getenv("SALZ_LOCAL_COUNT_ROUND");

@@ -338,6 +338,27 @@ __global__ void __launch_bounds__(TT) k_init(const uint8_t *__restrict__ T, size
     hist_flush(sh, passes, hist, tl.b);
 }
 
+// Digit histograms of the `second` field of a packed list (the bag's reorder key).  grid = tiles
+__global__ void __launch_bounds__(TT) k_bag_hist(const uint64_t *__restrict__ keys, ListView lv, int logS, int passes,
+                                                 uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[MAXP * 256];
+    for (int i = threadIdx.x; i < passes * 256; i += TT) sh[i] = 0;
+    __syncthreads();
+    const TileLoc tl = locate(lv, blockIdx.x);
+    const uint32_t Smask = (1u << logS) - 1;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t idx = threadIdx.x + i * TT;
+        if (idx < tl.valid) {
+            const uint32_t kf = (uint32_t)(keys[tl.first + idx] >> logS) & Smask;
+            for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((kf >> (8 * ps)) & 255u)], 1u);
+        }
+    }
+    __syncthreads();
+    hist_flush(sh, passes, hist, tl.b);
+}
+
 // digitBase[b][pass][d] = exclusive scan of hist[b][pass][*].  grid = (passes, B)
 // identMask (optional): bit `pass` is cleared unless ONE digit holds every element of the
 // block's list in that pass.  A pass whose bit survives for all blocks is the identity
@@ -1260,8 +1281,8 @@ __global__ void __launch_bounds__(TT, 3) k_rerank_apply(const uint64_t *__restri
             if (head[i] && head[i + 1]) {
                 if (!done) SA[gb + r] = p;
             } else {
-                if (PACKED) {
-                    stage[outLoc] = ((uint64_t)r << gShift) | p;
+                if (PACKED) {   // second field: a reorder key, equal for all members of the group
+                    stage[outLoc] = ((uint64_t)r << gShift) | (gShift == 2 * logS ? ((uint64_t)(r & Smask) << logS) : 0ull) | p;
                 } else if (BAGOUT) {
                     keysOut[outBase + outLoc] = ((uint64_t)r << gShift) | p;
                 } else {
@@ -1673,6 +1694,10 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     }
     const uint32_t totalKeep = swarp[NW].keep;
     const uint32_t sbase = s_misc[5];
+    // text position of the head before my range (survivors carry their group head's position in
+    // the `second` field, which nothing reads between rounds: sa_build_local may reorder the bag
+    // by it so that planted repeats are processed in text order)
+    uint32_t curHeadP = (!WIDE && ex.head) ? ((uint32_t)sk[lphys((int)ex.head - 1)] & Smask) : 0u;
     __syncthreads();   // everyone has read the sorted neighbours: sk can take the survivors
 
     uint32_t sgid[WIDE ? LITEMS : 1];
@@ -1692,6 +1717,7 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             if (hd) curHead = j + 1;
             if ((pstBits >> i) & 1u) curPst = j + 1;
             const uint32_t p = (uint32_t)k[i] & Smask;
+            if (hd) curHeadP = p;
             // WIDE: sorting kept every group where it was (shifted to the front by the merge path)
             const uint32_t grp = WIDE ? sgid[i] : (uint32_t)(k[i] >> (2 * logS));
             const uint32_t r = grp + (curHead - curPst);
@@ -1699,7 +1725,7 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
             if (hd && hn) {
                 SA[gb + r] = p;
             } else {
-                sk[outIdx] = ((uint64_t)r << gShift) | p;
+                sk[outIdx] = ((uint64_t)r << gShift) | (WIDE ? 0ull : ((uint64_t)curHeadP << logS)) | p;
                 outIdx++;
             }
         }
@@ -1965,10 +1991,39 @@ int sa_build_local(SortCtx &s, int &rounds)
     uint32_t count = ws.h_counters[0], tiles = ws.h_counters[1];
     rounds = 0;
     uint32_t round = 1;
+    bool reordered = false;
     while (count > 0) {
         if (round > 27) {
             fprintf(stderr, "salz_cuda: prefix doubling failed to converge (round %u)\n", round);
             return -1;
+        }
+        // Deep repeats (a bag that is still a good part of the text after two doubling rounds: pairs
+        // of a planted repeat, tied until h passes the repeat's length): from here on every round
+        // gathers rank[p + h] and scatters rank[p] for the same suffixes, in suffix-array order, i.e.
+        // one 8-byte entry per 32-byte sector.  ONE stable radix sort of the bag by the text position
+        // of each group's head (left in the `second` field by the previous round) puts the pairs
+        // of a repeat in text order; groups stay contiguous, and the survivors of later rounds keep
+        // the order.  Three 16-byte passes over the bag once, against ~3 x less DRAM traffic in every
+        // later round.
+        if (!wide && !reordered && ws.bagReorder && round >= (uint32_t)ws.bagReorder && (uint64_t)count * 8 > bd.M) {
+            const int kp = (logS + 7) / 8;
+            const int other = (bufS + 1) % 3;
+            tilemap(s, vS, TILE, 1);
+            if (fetch_counters(s)) return -1;
+            const uint32_t tilesT = ws.h_counters[3];
+            CK(cudaMemsetAsync(ws.hist, 0, histBytes, s.st));
+            k_bag_hist<<<tilesT, TT, 0, s.st>>>(ws.keys[bufS], view(ws, vS), logS, kp, ws.hist);
+            k_scan_hist<<<dim3(kp, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase, nullptr, nullptr);
+            s.lc.launches += 2;
+            s.algBytes += (uint64_t)count * 8;
+            const int res = radix_sort<true>(s, vS, count, tilesT, kp, logS, bufS, other);
+            if (res < 0) return -1;
+            bufS = res;
+            tilemap(s, vS, LTILE, 0);
+            if (fetch_counters(s)) return -1;
+            if (add_sort_time(s)) return -1;
+            tiles = ws.h_counters[1];
+            reordered = true;
         }
         // buffers: the bag is in keys[bufS]; the other two take the next bag and the global list
         const int bufOut = (bufS + 1) % 3, bufL = (bufS + 2) % 3;

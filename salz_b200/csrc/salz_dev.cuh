@@ -56,6 +56,7 @@ struct Workspace {
     uint32_t *passDone;  // [Bmax][8] tiles that have finished (block, pass) in that launch
     int scatterMode;     // 0 = register-staged k_scatter, 1 = TMA-staged, 2 = TMA-staged + two keys per ranking step
     int localCountRound; // first doubling round whose k_local may rank small groups by counting (SALZ_LOCAL_COUNT_ROUND, 3)
+    int bagReorder;      // first doubling round before which a large bag is reordered by text position (SALZ_BAG_REORDER, 3; 0 = never)
     int round0Bits;      // > 0: cap on the round-0 key width (SALZ_R0_BITS; fewer radix passes, more left for the doubling rounds)
     int sortGroup;       // > 0: all passes of a sort in one launch, block groups of this many blocks (L2-resident)
     uint32_t *counters; // [16] device scalars: [0]=list length, [1]=tiles
