@@ -346,13 +346,15 @@ __global__ void __launch_bounds__(TT) k_bag_hist(const uint64_t *__restrict__ ke
     for (int i = threadIdx.x; i < passes * 256; i += TT) sh[i] = 0;
     __syncthreads();
     const TileLoc tl = locate(lv, blockIdx.x);
-    const uint32_t Smask = (1u << logS) - 1;
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t idx = threadIdx.x + i * TT;
         if (idx < tl.valid) {
-            const uint32_t kf = (uint32_t)(keys[tl.first + idx] >> logS) & Smask;
-            for (int ps = 0; ps < passes; ps++) atomicAdd(&sh[ps * 256 + ((kf >> (8 * ps)) & 255u)], 1u);
+            const uint64_t e = keys[tl.first + idx];
+            // digit positions of the reorder passes: the last one is pulled down so that it ends with
+            // the field (it overlaps its predecessor; LSD passes stay correct with overlapping digits)
+            for (int ps = 0; ps < passes; ps++)
+                atomicAdd(&sh[ps * 256 + ((uint32_t)(e >> min(logS + 8 * ps, 2 * logS - 8)) & 255u)], 1u);
         }
     }
     __syncthreads();
@@ -1821,7 +1823,7 @@ void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, u
 // in keys[src]; the other buffer is keys[dst].  Returns the buffer holding the result.
 template <bool PACKED>
 int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, int shift0, int src, int dst,
-               uint32_t skipMask = 0, int *vbuf = nullptr)
+               uint32_t skipMask = 0, int *vbuf = nullptr, int shiftCap = 1 << 30)
 {
     int vs = vbuf ? *vbuf : (src & 1), vd = vs ^ 1;   // value buffers of the pairs format
     Workspace &ws = s.ws;
@@ -1831,7 +1833,7 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
         // TMA-staged kernel.  sortGroup > 0: all passes in ONE launch, tickets block-group-major
         // (a group's lists stay in L2 from pass to pass); otherwise a launch per pass.
         const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(ws.numSMs * SALZ_TCTAS));
-        const bool fused = ws.sortGroup > 0 && passes > 1 && skipMask == 0;
+        const bool fused = ws.sortGroup > 0 && passes > 1 && skipMask == 0 && shiftCap == (1 << 30);
         CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
         if (fused) {
             const uint32_t tickets = tiles * (uint32_t)passes;
@@ -1847,7 +1849,7 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
             for (int ps = 0; ps < passes; ps++) {
                 if ((skipMask >> ps) & 1u) continue;
                 if (done) CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
-                const PassPlan pp = {nullptr, tiles, ps, shift0 + 8 * ps, nullptr};
+                const PassPlan pp = {nullptr, tiles, ps, std::min(shift0 + 8 * ps, shiftCap), nullptr};
                 launch_scatter_tma(ws.scatterMode, grid, s.st, ws.keys[src], ws.keys[dst], view(ws, v), pp, ws.digitBase, ws.tileState);
                 s.lc.launches += 1;
                 s.lc.sort_launches += 1;
@@ -1866,11 +1868,11 @@ int radix_sort(SortCtx &s, int v, uint32_t count, uint32_t tiles, int passes, in
             CK(cudaMemsetAsync(ws.tileState, 0, ((size_t)tiles + 1) * 256 * 4, s.st));
             if (s.matchAny)
                 k_scatter<PACKED, true><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[vs], ws.keys[dst], ws.vals[vd],
-                                                                  view(ws, v), tiles, shift0 + 8 * ps, ps, ws.digitBase,
+                                                                  view(ws, v), tiles, std::min(shift0 + 8 * ps, shiftCap), ps, ws.digitBase,
                                                                   ws.tileState);
             else
                 k_scatter<PACKED, false><<<grid, TT, smem, s.st>>>(ws.keys[src], ws.vals[vs], ws.keys[dst],
-                                                                   ws.vals[vd], view(ws, v), tiles, shift0 + 8 * ps, ps,
+                                                                   ws.vals[vd], view(ws, v), tiles, std::min(shift0 + 8 * ps, shiftCap), ps,
                                                                    ws.digitBase, ws.tileState);
             s.lc.launches += 1;
             s.lc.sort_launches += 1;
@@ -2016,7 +2018,7 @@ int sa_build_local(SortCtx &s, int &rounds)
             k_scan_hist<<<dim3(kp, bd.B), 256, 0, s.st>>>(ws.hist, ws.digitBase, nullptr, nullptr);
             s.lc.launches += 2;
             s.algBytes += (uint64_t)count * 8;
-            const int res = radix_sort<true>(s, vS, count, tilesT, kp, logS, bufS, other);
+            const int res = radix_sort<true>(s, vS, count, tilesT, kp, logS, bufS, other, 0, nullptr, 2 * logS - 8);
             if (res < 0) return -1;
             bufS = res;
             tilemap(s, vS, LTILE, 0);
