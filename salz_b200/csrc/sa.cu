@@ -1474,6 +1474,38 @@ __global__ void __launch_bounds__(LT, SALZ_LCTAS) k_local(const uint64_t *__rest
     if (s_misc[2] >= s_misc[3]) return;
     const int lo0 = lo;   // gid[] stays indexed by the window position an element was loaded at
 
+#ifndef SALZ_LOCAL_FAST
+#define SALZ_LOCAL_FAST 1
+#endif
+    if (SALZ_LOCAL_FAST && COUNT && !WIDE) {
+        // Nothing to do in this window?  Deep repeats keep pairs tied for many rounds: every
+        // member of every own group has the same second key (and no suffix ends inside h).  Then
+        // no group splits, every rank entry already holds its group id (a reader of this round
+        // that meets an older stamp takes `new`, which is that id), and the elements go to the
+        // next bag as they are: no sort, no re-rank, no rank or SA stores.
+        const int jb = tid * LITEMS;
+        bool changed = false;
+        uint64_t last = (jb > lo && jb < hi) ? sk[lphys(jb - 1)] : 0;
+#pragma unroll
+        for (int i = 0; i < LITEMS; i++) {
+            const int j = jb + i;
+            if (j >= lo && j < hi) {
+                const uint64_t cur = sk[lphys(j)];
+                if (((uint32_t)(cur >> logS) & Smask) == 0) changed = true;                       // the suffix ends within h
+                if (j > lo && (last >> (2 * logS)) == (cur >> (2 * logS)) && (last >> logS) != (cur >> logS)) changed = true;
+                last = cur;
+            }
+        }
+        if (!__syncthreads_or(changed ? 1 : 0)) {
+            const uint32_t cntOwn = (uint32_t)(hi - lo);
+            if (tid == 0) s_misc[5] = atomicAdd(&cntS[tl.b], cntOwn);
+            __syncthreads();
+            const uint32_t sb = s_misc[5];
+            for (uint32_t i = tid; i < cntOwn; i += LT) outS[gb + sb + i] = sk[lphys(lo + (int)i)];
+            return;
+        }
+    }
+
     if (WIDE) {
         // the own groups get their index in the window as the group field of the key: heads of
         // my 16 consecutive positions, exclusive count over the threads before me
