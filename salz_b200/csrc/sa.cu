@@ -2026,6 +2026,7 @@ int sa_build_local(SortCtx &s, int &rounds)
     rounds = 0;
     uint32_t round = 1;
     bool reordered = false;
+    uint32_t prevCountL = 0xffffffffu;   // elements the previous round forwarded to the global path
     while (count > 0) {
         if (round > 27) {
             fprintf(stderr, "salz_cuda: prefix doubling failed to converge (round %u)\n", round);
@@ -2039,7 +2040,8 @@ int sa_build_local(SortCtx &s, int &rounds)
         // of a repeat in text order; groups stay contiguous, and the survivors of later rounds keep
         // the order.  Three 16-byte passes over the bag once, against ~3 x less DRAM traffic in every
         // later round.
-        if (!wide && !reordered && ws.bagReorder && round >= (uint32_t)ws.bagReorder && (uint64_t)count * 8 > bd.M) {
+        if (!wide && !reordered && ws.bagReorder && round >= (uint32_t)ws.bagReorder && (uint64_t)count * 8 > bd.M &&
+            (uint64_t)prevCountL * 8 < count) {   // ... and made of small groups: few elements took the global path
             const int kp = (logS + 7) / 8;
             const int other = (bufS + 1) % 3;
             tilemap(s, vS, TILE, 1);
@@ -2105,6 +2107,7 @@ int sa_build_local(SortCtx &s, int &rounds)
         }
         count = ws.h_counters[0];
         tiles = ws.h_counters[1];
+        prevCountL = countL;
         bufS = bufOut;
         vS = vNext;
         round++;
