@@ -385,6 +385,7 @@ def verify_stream(orc, data, block_len, stream, sizes, nsample=8):
     others) of a framed stream against the compiled reference.  Returns (ok, blocks checked)."""
     recs, total = split_records(sizes)
     if total != len(stream):
+        print("bench.py: record sizes add up to %d B, the stream has %d B" % (total, len(stream)), file=sys.stderr)
         return False, []
     nb = len(sizes)
     picks = {0, nb - 1, int(np.argmax(sizes)), int(np.argmin(sizes))}
@@ -392,10 +393,15 @@ def verify_stream(orc, data, block_len, stream, sizes, nsample=8):
     ok = True
     for b in sorted(picks):
         off, ln = recs[b]
-        want = orc.encode(data[b * block_len: (b + 1) * block_len])
+        # the capacity the reference CLI hands to salz_encode_safe for EVERY block, the short tail
+        # included (ref programs/salzcli.c:129): with the tail's own salz_encoded_len_max a nearly
+        # incompressible tail makes the reference itself fail
+        want = orc.encode(data[b * block_len: (b + 1) * block_len], cap=4 + block_len + (block_len + 63) // 64 * 8)
         hdr = int.from_bytes(bytes(stream[off - 4: off]), "little")
         if hdr != ln or bytes(stream[off: off + ln]) != want:
             ok = False
+            print("bench.py: record %d differs from the reference (framed length %d, record %d B, reference %s B)"
+                  % (b, hdr, ln, len(want) if want is not None else None), file=sys.stderr)
     return ok, sorted(picks)
 
 

@@ -230,6 +230,27 @@ def test_pipelined_host_stream_paths(orc):
             e.close()
 
 
+def test_incompressible_tail_block_is_plain_like_the_cli(enc, orc):
+    """A short, nearly incompressible tail block whose SALZ form overshoots ITS OWN
+    salz_encoded_len_max by a few bytes (a factor saves two direct bytes but can open one more
+    8-byte bit word): the reference CLI hands every block the capacity of a full block (ref
+    programs/salzcli.c:129), so it writes the tail as PLAIN; salz_encode_safe with the tail's own
+    capacity fails.  The stream entry follows the CLI, the block entry the API."""
+    bl = 1 << 16
+    tail = synth.uniform_random(4096, seed=3128)   # the tail of bench.py's 1 GiB mixed stream
+    full_cap = salz_b200.encoded_len_max(bl)
+    assert orc.encode(tail) is None and len(orc.encode(tail, cap=full_cap)) == 4100
+    data = np.concatenate([synth.english_like(2 * bl, seed=71), tail])
+    stream, sizes = enc.encode_stream(data, bl)
+    want = b""
+    for off in range(0, len(data), bl):
+        blk = orc.encode(data[off: off + bl], cap=full_cap)
+        want += len(blk).to_bytes(4, "little") + blk
+    assert sizes.tolist()[-1] == 4100 and stream == want
+    assert enc.encode(tail) is None                              # per-block API: the tail's own capacity, like the reference
+    assert enc.encode(tail, cap=full_cap) == orc.encode(tail, cap=full_cap)
+
+
 def test_stream_rejects_tiny_tail(enc):
     bl = 1 << 15
     with pytest.raises(salz_b200.SalzCudaError):
