@@ -359,7 +359,6 @@ static int stream_common(salz_cuda_ctx *c, const uint8_t *src, bool srcOnDevice,
 // kernels of batch i.  A stream that would fit one batch is cut in two for the same reason.
 // (Pageable host memory makes the copies synchronous; the result is the same.)
 constexpr int SPLIT_PCT = 25;  // share of a one-batch stream that goes into its first piece
-constexpr int SPLIT_LAST_PCT = 0;   // ... and into a third, last piece (0 = two pieces)
 
 static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, size_t block_len, uint8_t *dst,
                        size_t dst_cap, size_t *dst_len, uint32_t *block_sizes, size_t *nblocks_out)
@@ -381,10 +380,6 @@ static int stream_host(salz_cuda_ctx *c, const uint8_t *src, size_t src_len, siz
     if (cut.size() == 2 && nblocks >= 32) {
         static const int pct = [] { const char *e = getenv("SALZ_SPLIT_PCT"); int v = e ? atoi(e) : 0; return (v > 0 && v < 100) ? v : SPLIT_PCT; }();
         cut.insert(cut.begin() + 1, std::max<size_t>(16, nblocks * pct / 100));
-        // optionally a small LAST piece as well: its download is the copy nothing hides
-        static const int last = [] { const char *e = getenv("SALZ_SPLIT_LAST_PCT"); int v = e ? atoi(e) : 0; return (v > 0 && v < 50) ? v : SPLIT_LAST_PCT; }();
-        const size_t lastBlocks = nblocks * last / 100;
-        if (last > 0 && lastBlocks >= 16 && cut[1] + 16 + lastBlocks <= nblocks) cut.insert(cut.begin() + 2, nblocks - lastBlocks);
     }
     const size_t nbatch = cut.size() - 1;
     auto batch_off = [&](size_t i) { return cut[i] * block_len; };
