@@ -213,12 +213,15 @@ int salz_decode_safe(const uint8_t *src, size_t src_len, uint8_t *dst, size_t *d
         }
         if (s.p >= s.end)
             return -1;
-        const size_t offs = (((size_t)hi << 8) | *s.p++) + 1;
+        /* 32-bit arithmetic as in the reference (lib/salz.c:1101-1124): an over-long vnibble wraps */
+        const uint32_t offs = ((hi << 8) | *s.p++) + 1u;
         uint32_t q, low;
         if (!take_unary(&s, &q) || !take_bits(&s, 3, &low))
             return -1;
-        const size_t len = (((size_t)q << 3) | low) + 3;
-        if (len > cap - out || offs > out)
+        const uint32_t len = ((q << 3) | low) + 3u;
+        /* the reference does not check the offset against the bytes produced so far and reads
+         * before its output buffer (undefined); such streams are rejected here */
+        if (len > cap - out || offs > out || offs == 0)
             return -1;
         if (offs >= len) {
             memcpy(dst + out, dst + out - offs, len);

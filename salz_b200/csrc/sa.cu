@@ -641,22 +641,6 @@ __device__ __forceinline__ uint32_t ld_acquire(const uint32_t *p)
 }
 // barrier among the consumer warps only (the producer warp never joins it)
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(TT) : "memory"); }
-// k_scatter_tma<5>: barrier 2 = the 256 threads that scan the digit totals (arrive) -> look-back warp
-// (sync); barrier 3 = look-back warp (arrive) -> all consumers (sync): the tile's global bases are there
-__device__ __forceinline__ void lb_totals_arrive() { asm volatile("bar.arrive 2, 288;" ::: "memory"); }
-__device__ __forceinline__ void lb_totals_wait() { asm volatile("bar.sync 2, 288;" ::: "memory"); }
-__device__ __forceinline__ void lb_bases_arrive() { asm volatile("bar.arrive 3, %0;" ::"n"(TT + 32) : "memory"); }
-__device__ __forceinline__ void lb_bases_wait() { asm volatile("bar.sync 3, %0;" ::"n"(TT + 32) : "memory"); }
-__device__ __forceinline__ uint4 ld_relaxed_v4(const uint32_t *p)
-{
-    uint4 v;
-    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed_v4(uint32_t *p, uint4 v)
-{
-    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
 
 // -DSALZ_SCATTER_PROF: thread 0 of every CTA accumulates the cycles between the marks of a tile;
 // CTAs 0 and 150 print their sums at exit (A/B builds only: profiles/r02_scatter_phases.txt).
@@ -678,7 +662,7 @@ __device__ __forceinline__ void st_relaxed_v4(uint32_t *p, uint4 v)
 #endif
 
 template <int RANK2>
-__global__ void __launch_bounds__((RANK2 == 5 || RANK2 == 7) ? TTHREADS + 32 : TTHREADS, SALZ_TCTAS)
+__global__ void __launch_bounds__(TTHREADS, SALZ_TCTAS)
 k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const uint32_t *__restrict__ digitBase,
               uint32_t *tileState)
 {
@@ -704,17 +688,8 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = tid; i < 3 * WARPS * 256; i += (int)blockDim.x) wcnt[i] = 0;   // counts and both mask arrays
+    for (int i = tid; i < 3 * WARPS * 256; i += TTHREADS) wcnt[i] = 0;   // counts and both mask arrays
     __syncthreads();
-    constexpr bool ONEPASS = (RANK2 >= 2 && RANK2 <= 4);
-    constexpr bool LBWARP = (RANK2 == 5 || RANK2 == 7);   // a warp of its own does the look-back while the others rank
-    // peer masks from 8 votes on the digit bits, kept in registers from the counting to the ranking:
-    // one shared-memory atomic per GROUP of equal digits (its first lane) instead of two per key
-    constexpr bool BAL = (RANK2 == 6 || RANK2 == 7);
-    // the same with the masks built once by shared-memory atomicOr (alternating mask arrays), while counting
-    constexpr bool AOR = (RANK2 == 8);
-    constexpr bool REGMASK = BAL || AOR;
-    uint32_t *tot = maskB;                  // [256] LBWARP: digit totals of the tile (the second mask array is idle)
 
     if (warp == WARPS) {
         // ---- producer warp (one lane): tickets, tile descriptors, dependencies, bulk copies ----
@@ -752,71 +727,6 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
     }
 
-    if (LBWARP && warp == WARPS + 1) {
-        // ---- look-back warp: lane l owns digits 8l .. 8l+7 (two 16-byte state loads per tile) ----
-        constexpr int W = 4;   // predecessor tiles per round trip
-        constexpr uint32_t TAGMASK = 15u << ST_TAG_SHIFT;
-        for (uint32_t it = 0;; it++) {
-            const int k = it % TSLOTS;
-            mbar_wait(&full[k], (it / TSLOTS) & 1);
-            const uint32_t *sd = sdesc + 8 * k;
-            if (sd[0] >= pp.numTickets) return;
-            const uint32_t tile = sd[1], ps = sd[2], b = sd[3], lt = sd[4], valid = sd[6];
-            const uint32_t tag = (ps + 1) << ST_TAG_SHIFT;
-            // what does not depend on the tile's counts is fetched while the consumers count
-            const uint32_t *db = digitBase + ((size_t)b * MAXP + pp.pass0 + ps) * 256 + lane * 8;
-            const uint4 db0 = *(const uint4 *)db, db1 = *(const uint4 *)(db + 4);
-            const uint32_t lbase = lv.base[b];
-            uint32_t prev[8];
-#pragma unroll
-            for (int i = 0; i < 8; i++) prev[i] = 0;
-            lb_totals_wait();   // tot[] and dstart[] of this tile are complete
-            if (lt != 0) {
-                uint32_t t = tile - 1;
-                for (bool done = false; !done;) {
-                    const uint32_t w = min((uint32_t)W, lt - (tile - 1 - t));   // stay inside the block
-                    uint4 a[W], c[W];
-#pragma unroll
-                    for (int q = 0; q < W; q++) {
-                        if ((uint32_t)q < w) {
-                            const uint32_t *sp = state + (size_t)(t - q) * 256 + lane * 8;
-                            a[q] = ld_relaxed_v4(sp);
-                            c[q] = ld_relaxed_v4(sp + 4);
-                        } else a[q] = c[q] = make_uint4(0, 0, 0, 0);
-                    }
-#pragma unroll
-                    for (int q = 0; q < W; q++) {
-                        if (done || (uint32_t)q >= w) break;
-                        const uint32_t orw = a[q].x | a[q].y | a[q].z | a[q].w | c[q].x | c[q].y | c[q].z | c[q].w;
-                        const uint32_t andw = a[q].x & a[q].y & a[q].z & a[q].w & c[q].x & c[q].y & c[q].z & c[q].w;
-                        // all eight words published for this pass and of one kind (a tile caught while it
-                        // replaces its aggregates by inclusive prefixes is read again)
-                        if (((orw ^ tag) & TAGMASK) || ((andw ^ tag) & TAGMASK) || ((orw ^ andw) >> 30)) break;
-                        prev[0] += a[q].x & ST_VAL_MASK; prev[1] += a[q].y & ST_VAL_MASK;
-                        prev[2] += a[q].z & ST_VAL_MASK; prev[3] += a[q].w & ST_VAL_MASK;
-                        prev[4] += c[q].x & ST_VAL_MASK; prev[5] += c[q].y & ST_VAL_MASK;
-                        prev[6] += c[q].z & ST_VAL_MASK; prev[7] += c[q].w & ST_VAL_MASK;
-                        t--;
-                        if ((orw >> 30) == 2) done = true;
-                    }
-                }
-                uint4 t0 = *(const uint4 *)(tot + lane * 8), t1 = *(const uint4 *)(tot + lane * 8 + 4);
-                if (lane == 31) t1.w -= TILE - valid;   // the padding keys of a short tile sit in digit 255
-                const uint32_t f = LB_INCL | tag;
-                uint32_t *sp = state + (size_t)tile * 256 + lane * 8;
-                st_relaxed_v4(sp, make_uint4(f | (prev[0] + t0.x), f | (prev[1] + t0.y), f | (prev[2] + t0.z), f | (prev[3] + t0.w)));
-                st_relaxed_v4(sp + 4, make_uint4(f | (prev[4] + t1.x), f | (prev[5] + t1.y), f | (prev[6] + t1.z), f | (prev[7] + t1.w)));
-            }
-            const uint4 e0 = *(const uint4 *)(dstart + lane * 8), e1 = *(const uint4 *)(dstart + lane * 8 + 4);
-            *(uint4 *)(gbase + lane * 8) = make_uint4(lbase + db0.x + prev[0] - e0.x, lbase + db0.y + prev[1] - e0.y,
-                                                      lbase + db0.z + prev[2] - e0.z, lbase + db0.w + prev[3] - e0.w);
-            *(uint4 *)(gbase + lane * 8 + 4) = make_uint4(lbase + db1.x + prev[4] - e1.x, lbase + db1.y + prev[5] - e1.y,
-                                                          lbase + db1.z + prev[6] - e1.z, lbase + db1.w + prev[7] - e1.w);
-            __threadfence_block();
-            lb_bases_arrive();
-        }
-    }
-
     // ---- consumer warps ----
     uint32_t *mycnt = wcnt + warp * 256;
     uint32_t *myA = maskA + warp * 256, *myB = maskB + warp * 256;
@@ -849,8 +759,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             key[i] = (idx < tl.valid) ? skeys[idx] : ~0ull;
         }
         uint32_t lr[ITEMS / 2];       // RANK2 >= 2: warp-local ranks of a pair of keys, 16 bits each
-        uint32_t pm[REGMASK ? ITEMS : 1]; // REGMASK: peer mask of every key
-        if (ONEPASS) {
+        if (RANK2 >= 2) {
             // ONE peer-mask step per key: the rank of a key among the keys of its warp with the
             // same digit (running per-warp counter + lower peers) stays in a register, and the
             // counters end up as the warp's digit histogram.  No separate counting atomics, and
@@ -924,39 +833,6 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                 lr[j] = r0 | (r1 << 16);
                 __syncwarp();   // leaders' stores before the next step's atomics
             }
-        } else if (BAL) {
-#pragma unroll
-            for (int i = 0; i < ITEMS; i++) {
-                const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-                uint32_t m = 0xffffffffu;
-                if (__reduce_and_sync(0xffffffffu, d) != __reduce_or_sync(0xffffffffu, d)) {
-#pragma unroll
-                    for (int b = 0; b < 8; b++) {
-                        const bool bit = (d >> b) & 1u;
-                        const uint32_t v = __ballot_sync(0xffffffffu, bit);
-                        m &= bit ? v : ~v;
-                    }
-                }
-                pm[i] = m;
-                if (lane == __ffs(m) - 1) atomicAdd(&mycnt[d], (uint32_t)__popc(m));
-            }
-        } else if (AOR) {
-#pragma unroll
-            for (int i = 0; i < ITEMS; i++) {
-                const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-                uint32_t *mk = (i & 1) ? myB : myA;
-                uint32_t m = 0xffffffffu;
-                if (__reduce_and_sync(0xffffffffu, d) != __reduce_or_sync(0xffffffffu, d)) {
-                    atomicOr(&mk[d], laneBit);
-                    __syncwarp();
-                    m = mk[d];
-                    __syncwarp();   // all peers have read the mask before its first lane clears it
-                    if (lane == __ffs(m) - 1) mk[d] = 0;
-                }
-                pm[i] = m;
-                if (lane == __ffs(m) - 1) atomicAdd(&mycnt[d], (uint32_t)__popc(m));
-            }
-            __syncwarp();
         } else {
         // early counts: published before the ranking so that successors find aggregates
 #pragma unroll
@@ -986,7 +862,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
 #pragma unroll
             for (int w = 0; w < WARPS; w++) {
                 const uint32_t c = wcnt[w * 256 + tid];
-                if (!REGMASK) wcnt[w * 256 + tid] = sum;
+                wcnt[w * 256 + tid] = sum;
                 sum += c;
             }
             total = sum;
@@ -1010,45 +886,17 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             for (int w = 0; w < 7; w++) wb += (w < warp) ? scratch[w] : 0u;
             ex += wb;
             dstart[tid] = ex;
-            if (REGMASK) {   // the counters become the staging positions themselves: digit start + warps before mine
-                uint32_t run = ex;
-#pragma unroll
-                for (int w = 0; w < WARPS; w++) {
-                    const uint32_t c = wcnt[w * 256 + tid];
-                    wcnt[w * 256 + tid] = run;
-                    run += c;
-                }
-            }
-            if (LBWARP) {
-                tot[tid] = total;
-                __threadfence_block();
-                lb_totals_arrive();
-            }
         }
         consumer_sync();
         PROF_MARK(4);
 
-        if (ONEPASS) {
+        if (RANK2 >= 2) {
             // the counters now hold the exclusive prefix over the warps before mine
 #pragma unroll
             for (int j = 0; j < ITEMS / 2; j++) {
                 const uint32_t d0 = dd[j] & 255u, d1 = dd[j] >> 8;
                 skeys[dstart[d0] + mycnt[d0] + (lr[j] & 0xffffu)] = key[2 * j];
                 skeys[dstart[d1] + mycnt[d1] + (lr[j] >> 16)] = key[2 * j + 1];
-            }
-            __syncwarp();
-        } else if (REGMASK) {
-            // the first lane of a group of equal digits advances the running position for the group
-            // (same-warp atomics on one address execute in program order: steps stay in tile order)
-#pragma unroll
-            for (int i = 0; i < ITEMS; i++) {
-                const uint32_t d = (uint32_t)(key[i] >> shift) & 255u;
-                const uint32_t m = pm[i];
-                const int leader = __ffs(m) - 1;
-                uint32_t c = 0;
-                if (lane == leader) c = atomicAdd(&mycnt[d], (uint32_t)__popc(m));
-                c = __shfl_sync(0xffffffffu, c, leader);
-                skeys[c + __popc(m & lt_mask)] = key[i];
             }
             __syncwarp();
         } else
@@ -1067,7 +915,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                     if (d0 == d1) mycnt[d0] = c0 + 64;
                     else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
                 }
-            } else if (RANK2 == 1) {   // two keys per step, two mask arrays: the round trips of a step overlap
+            } else if (RANK2) {   // two keys per step, two mask arrays: the round trips of a step overlap
                 atomicOr(&myA[d0], laneBit);
                 atomicOr(&myB[d1], laneBit);
                 __syncwarp();
@@ -1105,7 +953,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         for (int i = lane; i < 256; i += 32) mycnt[i] = 0;
         PROF_MARK(5);
 
-        if (!LBWARP && tid < 256) {
+        if (tid < 256) {
             uint32_t prev = 0;
             if (tl.lt != 0) {
                 uint32_t t = tile - 1;
@@ -1130,8 +978,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             gbase[tid] = lv.base[tl.b] + digitBase[((size_t)tl.b * MAXP + pp.pass0 + ps) * 256 + tid] + prev - ex;
         }
         PROF_MARK(6);
-        if (LBWARP) lb_bases_wait();   // staged keys of all warps + the look-back warp's gbase[]
-        else consumer_sync();
+        consumer_sync();
         PROF_MARK(7);
 
         for (uint32_t j = tid; j < tl.valid; j += TT) {
@@ -1991,10 +1838,7 @@ int fetch_counters(SortCtx &s)
 
 // SALZ_SCATTER: 1 = counts first, then ranking; 2 = the same with two keys per ranking step;
 // 3 = one ranking pass, warp-local ranks kept in registers; 4 = the same, two keys per step;
-// 5 = one ranking pass with peer masks from 8 votes on the digit bits (no mask arrays);
-// 6 = as 1, with the decoupled look-back in a warp of its own, under the ranking;
-// 7 = counts and ranks from vote-built peer masks kept in registers (one shared atomic per group of
-// equal digits); 8 = 7 + look-back warp; 9 = as 7 with the masks built by shared-memory atomicOr
+// 5 = one ranking pass with peer masks from 8 votes on the digit bits (no mask arrays)
 void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, uint64_t *b, const ListView &lv,
                         const PassPlan &pp, const uint32_t *digitBase, uint32_t *tileState)
 {
@@ -2003,10 +1847,6 @@ void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, u
     case 3: k_scatter_tma<2><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     case 4: k_scatter_tma<3><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     case 5: k_scatter_tma<4><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
-    case 6: k_scatter_tma<5><<<grid, TTHREADS + 32, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
-    case 7: k_scatter_tma<6><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
-    case 8: k_scatter_tma<7><<<grid, TTHREADS + 32, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
-    case 9: k_scatter_tma<8><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     default: k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState); break;
     }
 }
@@ -2296,10 +2136,6 @@ int sa_init_device()
     CK(cudaFuncSetAttribute(k_scatter_tma<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     return 0;
 }
 
