@@ -25,7 +25,7 @@ def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    defs = ["-D%s=%s" % (k, os.environ[k]) for k in ("SALZ_TT", "SALZ_ITEMS", "SALZ_LBW", "SALZ_LT", "SALZ_LITEMS", "SALZ_LCTAS", "SALZ_PC", "SALZ_HELPERS", "SALZ_PARSE_CTAS", "SALZ_NCH", "SALZ_PER", "SALZ_PLCP_CTAS", "SALZ_SCTAS", "SALZ_PLCP_ITEMS", "SALZ_WARM", "SALZ_TCTAS", "SALZ_TSLOTS", "SALZ_L2_HINTS", "SALZ_SCATTER_PROF", "SALZ_LOCAL_FAST") if k in os.environ]
+    defs = ["-D%s=%s" % (k, os.environ[k]) for k in ("SALZ_TT", "SALZ_ITEMS", "SALZ_LBW", "SALZ_LT", "SALZ_LITEMS", "SALZ_LCTAS", "SALZ_PC", "SALZ_HELPERS", "SALZ_PARSE_CTAS", "SALZ_NCH", "SALZ_PER", "SALZ_PLCP_CTAS", "SALZ_SCTAS", "SALZ_PLCP_ITEMS", "SALZ_WARM", "SALZ_TCTAS", "SALZ_TSLOTS", "SALZ_L2_HINTS", "SALZ_SCATTER_PROF", "SALZ_LOCAL_FAST", "SALZ_AL") if k in os.environ]
     cmd = [nvcc] + NVCC_FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + \
           ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     subprocess.run(cmd, check=True)

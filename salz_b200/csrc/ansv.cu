@@ -31,8 +31,12 @@ struct Pyr {
     int logS;
 };
 
-constexpr int AL = 32;              // slots per segment (one thread)
-constexpr int AT = 128;             // threads = segments per tile
+#ifndef SALZ_AL
+#define SALZ_AL 32
+#endif
+constexpr int AL = SALZ_AL;         // slots per segment (one thread): 32 or 16
+constexpr int AT = 4096 / AL;       // threads = segments per tile
+constexpr int APR = 32 / AL;        // segments per group of the level-1 pyramid (32 slots)
 constexpr int ATS = AL * AT;        // slots per tile
 constexpr int APAD = AL + 1;        // padded segment stride in shared memory
 constexpr int32_t AINF = 0x7fffffff;
@@ -64,11 +68,13 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
     const uint32_t n = blkN[b] - 8;
     const uint32_t t0 = tb * ATS;  // first slot of the tile (local)
     const size_t gb = (size_t)b << logS;
-    const size_t pyr1 = ((gb + t0) >> 5) + tid;  // my segment is one group of the level-1 pyramid
+    const size_t pyr1 = ((gb + t0) >> 5) + tid / APR;  // APR segments make one group of the level-1 pyramid
     if (t0 >= n) {
         if (tid == 0) { tileMinV[blockIdx.x] = AINF; tileMinL[blockIdx.x] = AINF; }
-        pyrSA1[pyr1] = AINF;
-        pyrLCP1[pyr1] = AINF;
+        if (tid % APR == 0) {
+            pyrSA1[pyr1] = AINF;
+            pyrLCP1[pyr1] = AINF;
+        }
         return;
     }
     int2 *cd = cand2 + 2 * gb;
@@ -94,7 +100,7 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
 #pragma unroll
         for (int u = 0; u < LDB; u++) {
             const int j = (base + u) * AT + tid;
-            const int k = (j >> 5) * APAD + (j & 31);
+            const int k = (j / AL) * APAD + (j % AL);
             sv[k] = a[u] << 8;
             sm[k] = l[u];
         }
@@ -139,17 +145,30 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         segLen[tid] = (uint8_t)len;
         segMin[tid] = (lastPM >= 0) ? (int32_t)(sv[sb + lastPM] >> 8) : AINF;
         segLcp[tid] = lmin;
-        pyrSA1[pyr1] = segMin[tid];  // minima over 32 consecutive SA slots (AINF past n): level 1 of the
-        pyrLCP1[pyr1] = lmin;        // pyramids k_ansv_far walks
+        // minima over 32 consecutive SA slots (AINF past n): level 1 of the pyramids k_ansv_far walks
+        int32_t gv = segMin[tid], gl = lmin;
+#pragma unroll
+        for (int o = 1; o < APR; o <<= 1) {
+            gv = min(gv, __shfl_xor_sync(0xffffffffu, gv, o));
+            gl = min(gl, __shfl_xor_sync(0xffffffffu, gl, o));
+        }
+        if (tid % APR == 0) {
+            pyrSA1[pyr1] = gv;
+            pyrLCP1[pyr1] = gl;
+        }
     }
     __syncthreads();
     // exclusive prefix / suffix minima over the tile's segments: an element smaller
     // than everything on one side skips the search (monotone SA: every element)
     if (tid < 32) {
-        int32_t v[4], l[4];
+        constexpr int K = AT / 32;   // segments per lane
+        int32_t v[K], l[K];
+        int32_t av = AINF, al = AINF;
 #pragma unroll
-        for (int k = 0; k < 4; k++) { v[k] = segMin[tid * 4 + k]; l[k] = segLcp[tid * 4 + k]; }
-        int32_t av = min(min(v[0], v[1]), min(v[2], v[3])), al = min(min(l[0], l[1]), min(l[2], l[3]));
+        for (int k = 0; k < K; k++) {
+            v[k] = segMin[tid * K + k]; l[k] = segLcp[tid * K + k];
+            av = min(av, v[k]); al = min(al, l[k]);
+        }
         int32_t pv = av, pl = al, sv_ = av, sl = al;  // inclusive scans over lanes
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -162,15 +181,15 @@ __global__ void __launch_bounds__(AT) k_ansv_tile(const uint32_t *__restrict__ S
         int32_t ev = __shfl_up_sync(0xffffffffu, pv, 1), el = __shfl_up_sync(0xffffffffu, pl, 1);
         if (tid == 0) { ev = AINF; el = AINF; }
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            preV[tid * 4 + k] = ev; preL[tid * 4 + k] = el;
+        for (int k = 0; k < K; k++) {
+            preV[tid * K + k] = ev; preL[tid * K + k] = el;
             ev = min(ev, v[k]); el = min(el, l[k]);
         }
         ev = __shfl_down_sync(0xffffffffu, sv_, 1); el = __shfl_down_sync(0xffffffffu, sl, 1);
         if (tid == 31) { ev = AINF; el = AINF; }
 #pragma unroll
-        for (int k = 3; k >= 0; k--) {
-            sufV[tid * 4 + k] = ev; sufL[tid * 4 + k] = el;
+        for (int k = K - 1; k >= 0; k--) {
+            sufV[tid * K + k] = ev; sufL[tid * K + k] = el;
             ev = min(ev, v[k]); el = min(el, l[k]);
         }
     }
