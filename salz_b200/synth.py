@@ -208,3 +208,64 @@ def small_cases(seed=0):
             base[d: d + L] = base[s: s + L]
         cases.append(("planted%d" % i, base))
     return cases
+
+
+def fibonacci_word(n):
+    """Prefix of the infinite Fibonacci word over {a, b}: the classic worst case of repeat-rich text
+    (every prefix doubling round keeps almost all suffixes tied)."""
+    a, b = b"a", b"ab"
+    while len(b) < n:
+        a, b = b, b + a
+    return np.frombuffer(b[:n], np.uint8).copy()
+
+
+def thue_morse(n):
+    """Thue-Morse word (cube-free, but full of squares at every scale)."""
+    x = np.arange(n, dtype=np.uint64)
+    par = np.zeros(n, np.uint8)
+    while x.any():
+        par ^= (x & 1).astype(np.uint8)
+        x >>= 1
+    return par + 97
+
+
+def de_bruijn(k, n):
+    """de Bruijn sequence B(k, n): every n-gram over k symbols exactly once (no repeat longer than n - 1)."""
+    a = [0] * (k * n)
+    seq = []
+
+    def db(t, p):
+        if t > n:
+            if n % p == 0:
+                seq.extend(a[1:p + 1])
+        else:
+            a[t] = a[t - p]
+            db(t + 1, p)
+            for j in range(a[t - p] + 1, k):
+                a[t] = j
+                db(t + 1, t)
+
+    db(1, 1)
+    return np.array(seq, np.uint8) + 65
+
+
+def growing_runs(n):
+    """a b aa b aaa b ...: runs of every length, each a prefix of the next."""
+    out, k, tot = [], 1, 0
+    while tot < n:
+        out.append(np.full(k, 97, np.uint8))
+        out.append(np.array([98], np.uint8))
+        tot += k + 1
+        k += 1
+    return np.concatenate(out)[:n]
+
+
+def adversarial_cases(scale=1):
+    """Inputs with suffix structure that prefix doubling finds hard; sizes multiply with `scale`."""
+    defect = np.resize(np.frombuffer(b"abcabcabd", np.uint8), 250000 * scale).copy()
+    defect[len(defect) // 2] = 120          # one defect in the middle of a long period
+    two = np.concatenate([fibonacci_word(120000 * scale), thue_morse(90000 * scale), fibonacci_word(100000 * scale)])
+    return [("fibonacci", fibonacci_word(300000 * scale)), ("thue_morse", thue_morse(300000 * scale)),
+            ("de_bruijn_4_9", de_bruijn(4, 9)), ("growing_runs", growing_runs(200000 * scale)),
+            ("sorted_bytes", np.resize(np.arange(256, dtype=np.uint8), 150000 * scale)),
+            ("period_defect", defect), ("fib_thue_fib", two)]

@@ -109,6 +109,28 @@ def test_medium_cases_all_stages(enc, orc):
         _check_stages(enc, orc, name, data)
 
 
+def test_adversarial_suffix_structures(enc, orc):
+    """Fibonacci and Thue-Morse words, a de Bruijn sequence, runs of every length, a long period with
+    one defect: many doubling rounds, groups that cross every window, the bag reorder and the
+    unchanged-window fast path, one-chain parses.  All stages against the reference; then the same
+    inputs as ONE ragged batch (different alphabets and round-0 key widths per block), and in a
+    context whose block capacity is above 2^21 (wide elements, pairs on the global path)."""
+    cases = synth.adversarial_cases()
+    for name, data in cases:
+        _check_stages(enc, orc, name, data)
+    big = synth.fibonacci_word(1 << 20)
+    assert enc.encode(big) == orc.encode(big), "fibonacci 1 MiB"
+    outs = enc.encode_blocks([c[1] for c in cases])
+    for (name, data), got in zip(cases, outs):
+        assert got == orc.encode(data), ("batched", name)
+    e = salz_b200.SalzCuda(0, 1 << 22, 2)
+    try:
+        for name, data in cases[:4] + [("fibonacci3M", synth.fibonacci_word(3 << 20))]:
+            assert e.encode(data) == orc.encode(data), ("wide", name)
+    finally:
+        e.close()
+
+
 @pytest.mark.parametrize("k", [1, 2, 8, 64, -4, -64])
 def test_parse_segments_exact_for_every_cut(enc, orc, k):
     """The segmented parse (estimates to the right of a segment, passes until nothing
