@@ -727,6 +727,10 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
     }
 
+    // two-phase modes: the running counters start at digit start + warps before mine, so a key's
+    // staging position needs no separate digit-start look-up (one random shared-memory access less
+    // per key: sort 10.12 -> 9.90 ms per step)
+    constexpr bool FOLD = (RANK2 <= 1);
     // ---- consumer warps ----
     uint32_t *mycnt = wcnt + warp * 256;
     uint32_t *myA = maskA + warp * 256, *myB = maskB + warp * 256;
@@ -759,7 +763,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             key[i] = (idx < tl.valid) ? skeys[idx] : ~0ull;
         }
         uint32_t lr[ITEMS / 2];       // RANK2 >= 2: warp-local ranks of a pair of keys, 16 bits each
-        if (RANK2 >= 2) {
+        if (RANK2 >= 2 && RANK2 <= 4) {
             // ONE peer-mask step per key: the rank of a key among the keys of its warp with the
             // same digit (running per-warp counter + lower peers) stays in a register, and the
             // counters end up as the warp's digit histogram.  No separate counting atomics, and
@@ -862,7 +866,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
 #pragma unroll
             for (int w = 0; w < WARPS; w++) {
                 const uint32_t c = wcnt[w * 256 + tid];
-                wcnt[w * 256 + tid] = sum;
+                if (!FOLD) wcnt[w * 256 + tid] = sum;
                 sum += c;
             }
             total = sum;
@@ -886,11 +890,20 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             for (int w = 0; w < 7; w++) wb += (w < warp) ? scratch[w] : 0u;
             ex += wb;
             dstart[tid] = ex;
+            if (FOLD) {
+                uint32_t run = ex;
+#pragma unroll
+                for (int w = 0; w < WARPS; w++) {
+                    const uint32_t c = wcnt[w * 256 + tid];
+                    wcnt[w * 256 + tid] = run;
+                    run += c;
+                }
+            }
         }
         consumer_sync();
         PROF_MARK(4);
 
-        if (RANK2 >= 2) {
+        if (RANK2 >= 2 && RANK2 <= 4) {
             // the counters now hold the exclusive prefix over the warps before mine
 #pragma unroll
             for (int j = 0; j < ITEMS / 2; j++) {
@@ -915,7 +928,7 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                     if (d0 == d1) mycnt[d0] = c0 + 64;
                     else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
                 }
-            } else if (RANK2) {   // two keys per step, two mask arrays: the round trips of a step overlap
+            } else if (RANK2 == 1) {   // two keys per step, two mask arrays: the round trips of a step overlap
                 atomicOr(&myA[d0], laneBit);
                 atomicOr(&myB[d1], laneBit);
                 __syncwarp();
@@ -945,8 +958,8 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                 r1 = c1 + __popc(m1 & lt_mask);
                 if (lane == __ffs(m1) - 1) { myA[d1] = 0; mycnt[d1] = c1 + __popc(m1); }
             }
-            skeys[dstart[d0] + r0] = key[2 * j];
-            skeys[dstart[d1] + r1] = key[2 * j + 1];
+            skeys[(FOLD ? 0u : dstart[d0]) + r0] = key[2 * j];
+            skeys[(FOLD ? 0u : dstart[d1]) + r1] = key[2 * j + 1];
             __syncwarp();   // leaders' stores before the next step's atomics
         }
         // the warp's counters are its own again: cleared for the next tile
