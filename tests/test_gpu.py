@@ -7,6 +7,7 @@ import hashlib
 import json
 import os
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -129,6 +130,35 @@ def test_adversarial_suffix_structures(enc, orc):
             assert e.encode(data) == orc.encode(data), ("wide", name)
     finally:
         e.close()
+
+
+def test_order_check_fallback_path(tmp_path):
+    """The default radix ranking takes the slot returned by the counting atomicAdd and VERIFIES that
+    every pass was stable; if the check ever fails the suffix sort is repeated with the peer-mask
+    ranking.  The check does not fail on this hardware, so the repeat path is forced here, in a
+    process of its own (the switch is read once per process)."""
+    script = tmp_path / "fb.py"
+    script.write_text(
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "import salz_b200\n"
+        "from salz_b200 import synth\n"
+        "from oracle.binding import Ref\n"
+        "orc = Ref()\n"
+        "e = salz_b200.SalzCuda(0, 1 << 20, 4)\n"
+        "for d in (synth.english_like(700000, seed=3), synth.dna_like(300000, seed=4, block=300000), np.full(50000, 97, np.uint8)):\n"
+        "    assert e.encode(d) == orc.encode(d)\n"
+        "outs = e.encode_blocks([synth.english_like(1 << 20, seed=s) for s in (5, 6, 7)])\n"
+        "assert all(o == orc.encode(synth.english_like(1 << 20, seed=s)) for o, s in zip(outs, (5, 6, 7)))\n"
+        "print('ok')\n" % ROOT)
+    env = dict(os.environ, SALZ_FORCE_ORDER_FALLBACK="1")
+    p = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, env=env, timeout=600)
+    assert p.returncode == 0 and "ok" in p.stdout, p.stderr[-2000:]
+    assert "repeating with the peer-mask ranking" in p.stderr
+    # and without the switch nothing is repeated
+    p = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0 and "ok" in p.stdout, p.stderr[-2000:]
+    assert "repeating" not in p.stderr
 
 
 @pytest.mark.parametrize("k", [1, 2, 8, 64, -4, -64])
