@@ -129,9 +129,11 @@ void salz_cuda_host_free(void *p);
 int salz_cuda_get_stats(const salz_cuda_ctx *ctx, salz_cuda_stats *out);
 void salz_cuda_reset_stats(salz_cuda_ctx *ctx);
 
-/* Tunables (tests, A/B timing): ranking inside the radix scatter pass.
+/* Tunables (tests, A/B timing): ranking inside the register-staged radix scatter pass
+ * (pairs of blocks above 2 MiB, and SALZ_SCATTER=0).
  * mode 1 (default) = warp peer masks by shared-memory atomicOr,
- * mode 0           = warp peer masks by match_any. */
+ * mode 0           = warp peer masks by match_any.
+ * The TMA-staged pass of packed lists is chosen by the environment (SALZ_SCATTER). */
 void salz_cuda_set_sort_mode(salz_cuda_ctx *ctx, int mode);
 
 /* Segments per block of the optimal parse (replaces nothing in the reference:

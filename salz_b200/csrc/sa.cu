@@ -19,7 +19,10 @@
 //              look-back over per-tile digit counts, keys staged through
 //              shared memory in digit order and written back as coalesced runs;
 //              k_scatter_tma: tiles arrive by cp.async.bulk on an mbarrier ring, issued
-//              by a dedicated producer warp
+//              by a dedicated producer warp; tickets interleave the tiles of 64 blocks (64
+//              look-back chains side by side); default ranking: the slot returned by the
+//              counting atomicAdd, with a stability check in the write-out and a host
+//              fallback to the peer-mask ranking
 //   k_rerank_* adjacent-key compare + scan: new group ids; suffixes whose
 //              group became a singleton are written to SA and dropped
 //
