@@ -433,3 +433,77 @@ def emit_model(T, N, choice, jump):
     out[0:4] = hdr.to_bytes(4, "little"); written[0:4] += 1
     assert (written == 1).all(), "every output byte must be written exactly once"
     return bytes(out)
+
+
+# ---------------------------------------------------- sa.cu: radix pass ----
+def sched_interleave_model(tile_counts, group):
+    """k_sched_interleave: ticket order of a single-pass launch.  tile_counts[b] = tiles of block b
+    (tile ids are block-major).  Inside a group of `group` consecutive blocks tickets run over
+    (tile index in its block, block).  Returns sched (ticket -> tile id)."""
+    base = np.concatenate([[0], np.cumsum(tile_counts)]).astype(np.int64)
+    n = int(base[-1])
+    sched = np.full(n, -1, np.int64)
+    B = len(tile_counts)
+    for b in range(B):
+        g0 = b - b % group
+        g1 = min(g0 + group, B)
+        for lt in range(tile_counts[b]):
+            t = base[g0]
+            for bb in range(g0, g1):
+                cnt = tile_counts[bb]
+                t += min(cnt, lt) + (1 if (bb < b and cnt > lt) else 0)
+            assert sched[t] == -1
+            sched[t] = base[b] + lt
+    return sched
+
+
+def scatter_pass_model(keys, shift, tile=96, warps=3, lane_order=None):
+    """One stable 8-bit LSD pass over ONE block's list the way k_scatter_tma<5> does it (optimistic,
+    verified ranks).  Per tile: warp w holds tile indices w*W + step*32 + lane (W = tile / warps);
+    the counting atomicAdd of a step hands out slots of (warp, digit) in `lane_order` (None = lane
+    order, what the hardware does; anything else models hardware that serialises differently);
+    a key is staged as its tile index at digit start + warp prefix + slot; the write-out fetches
+    the keys through the staged indices and checks that the indices of every digit run increase.
+    Returns (keys after the pass, number of tiles whose order check failed)."""
+    keys = np.asarray(keys, np.uint64)
+    n = len(keys)
+    out = np.zeros(n, np.uint64)
+    dig_all = ((keys >> np.uint64(shift)) & np.uint64(255)).astype(np.int64)
+    digit_base = np.concatenate([[0], np.cumsum(np.bincount(dig_all, minlength=256))])[:256]
+    prev = np.zeros(256, np.int64)            # what the decoupled look-back delivers: earlier tiles' counts
+    per_warp = tile // warps
+    steps = per_warp // 32
+    unordered = 0
+    for t0 in range(0, n, tile):
+        valid = min(tile, n - t0)
+        tk = np.full(tile, np.uint64(2**64 - 1), np.uint64)    # padding keys: digit 255, after every real key
+        tk[:valid] = keys[t0:t0 + valid]
+        d = ((tk >> np.uint64(shift)) & np.uint64(255)).astype(np.int64)
+        cnt = np.zeros((warps, 256), np.int64)
+        slot = np.zeros(tile, np.int64)
+        for w in range(warps):
+            for s in range(steps):
+                lanes = list(range(32)) if lane_order is None else list(lane_order)
+                for lane in lanes:                              # the order in which the atomic unit serves the lanes
+                    i = w * per_warp + s * 32 + lane
+                    slot[i] = cnt[w, d[i]]
+                    cnt[w, d[i]] += 1
+        total = cnt.sum(axis=0)
+        dstart = np.concatenate([[0], np.cumsum(total)])[:256]
+        first = dstart[None, :] + np.cumsum(cnt, axis=0) - cnt   # digit start + warps before mine
+        sidx = np.full(tile, -1, np.int64)
+        for i in range(tile):
+            pos = first[i // per_warp, d[i]] + slot[i]
+            assert sidx[pos] == -1
+            sidx[pos] = i
+        bad = False
+        for j in range(valid):
+            si = sidx[j]
+            if si >= valid or (j > 0 and d[sidx[j - 1]] == d[si] and sidx[j - 1] >= si):
+                bad = True
+            dj = d[si]
+            out[digit_base[dj] + prev[dj] + (j - dstart[dj])] = tk[si]
+        unordered += bad
+        total[255] -= tile - valid
+        prev += total
+    return out, unordered

@@ -127,3 +127,47 @@ def test_chunk_entry_speculation_is_exact():
             want[e // chunk] = e
             e = int(jump[e])
         assert km.chunk_entries_model(jump, N, chunk, lanes) == want, (trial, chunk, lanes, N)
+
+
+def test_radix_pass_model_order_check_and_ticket_schedule():
+    """Design check of the default radix pass (sa.cu: k_scatter_tma<5>, k_sched_interleave) without a
+    GPU: slots handed out in lane order give a stable pass - five passes sort - and the order check
+    stays silent; slots handed out in any other order are caught by the check.  The interleaved
+    ticket schedule is a permutation in which every tile comes after its block's earlier tiles."""
+    rng = np.random.default_rng(7)
+    for kind in ("uniform", "skewed", "runs"):
+        n = 1000
+        if kind == "uniform":
+            keys = rng.integers(0, 1 << 40, n, dtype=np.uint64)
+        elif kind == "skewed":
+            keys = (rng.integers(0, 6, n, dtype=np.uint64) << np.uint64(32)) | (rng.integers(0, 3, n, dtype=np.uint64) << np.uint64(8)) | rng.integers(0, 2, n, dtype=np.uint64)
+        else:
+            keys = np.repeat(rng.integers(0, 1 << 40, n // 50, dtype=np.uint64), 50)
+        keys = (keys << np.uint64(20)) | np.arange(n, dtype=np.uint64)        # unique keys, like (group, second, p)
+        cur = keys.copy()
+        for ps in range(5):
+            cur, bad = km.scatter_pass_model(cur, 20 + 8 * ps)
+            assert bad == 0, (kind, ps)
+        assert np.array_equal(cur, np.sort(keys)), kind
+        # hardware that served the lanes of a step in another order: detected, tile by tile
+        rev, bad = km.scatter_pass_model(keys, 20, lane_order=range(31, -1, -1))
+        if kind != "uniform":      # equal digits inside a step are certain for these inputs
+            assert bad > 0, kind
+        shuf = list(rng.permutation(32))
+        _, bad2 = km.scatter_pass_model(keys, 20, lane_order=shuf)
+        if kind == "runs":
+            assert bad2 > 0
+    for counts, group in (([5, 5, 5, 5], 2), ([3, 0, 7, 1, 4], 4), ([6], 64), ([2, 9, 9, 1, 0, 3, 8], 3), ([4] * 10, 64)):
+        sched = km.sched_interleave_model(counts, group)
+        assert sorted(sched) == list(range(sum(counts)))
+        base = np.concatenate([[0], np.cumsum(counts)])
+        pos = np.empty(len(sched), np.int64)
+        pos[sched] = np.arange(len(sched))
+        for b, c in enumerate(counts):
+            for lt in range(1, c):
+                assert pos[base[b] + lt - 1] < pos[base[b] + lt]      # look-back predecessors claimed first
+        # groups stay in block order: every ticket of a group precedes every ticket of the next one
+        for g0 in range(group, len(counts), group):
+            lo, hi = pos[:base[g0]], pos[base[g0]:]
+            if len(lo) and len(hi):
+                assert lo.max() < hi.min()
