@@ -674,9 +674,9 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
     uint64_t *slot0 = (uint64_t *)smem;                  // [TSLOTS][TILE] arriving tile, then its keys in digit order
     uint32_t *wcnt = (uint32_t *)(slot0 + TSLOTS * TILE);   // [WARPS][256] per-warp digit counts -> running offsets
     uint32_t *maskA = wcnt + WARPS * 256;                // [WARPS][256] peer masks (self-cleaning)
-    uint32_t *maskB = maskA + WARPS * 256;               // [WARPS][256] second key of a pair
-    uint32_t *dstart = maskB + WARPS * 256;              // [256]
-    uint32_t *gbase = dstart + 256;                      // [256]
+    // (room for a second mask array and a digit-start table follows: experiments that are gone;
+    // the shared-memory size is part of the measured configuration)
+    uint32_t *gbase = maskA + 2 * WARPS * 256 + 256;     // [256]
     uint32_t *scratch = gbase + 256;                     // [16]
     uint32_t *sdesc = scratch + 16;                      // [TSLOTS][8] ticket, tile, pass, b, lt, first, valid
     uint64_t *full = (uint64_t *)(sdesc + 8 * 4);        // [TSLOTS] tile (and its descriptor) has arrived
@@ -731,10 +731,9 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
         }
     }
 
-    // two-phase modes: the running counters start at digit start + warps before mine, so a key's
-    // staging position needs no separate digit-start look-up (one random shared-memory access less
-    // per key: sort 10.12 -> 9.90 ms per step)
-    constexpr bool FOLD = (RANK2 <= 1) || (RANK2 == 5);
+    // The running counters start at digit start + warps before mine, so a key's staging position
+    // needs no separate digit-start look-up (one random shared-memory access less per key: sort
+    // 10.12 -> 9.90 ms per step with the peer-mask ranking).
     // RANK2 == 5, optimistic ranks: the counting atomicAdd RETURNS a slot that is unique among the
     // keys of (warp, digit), in instruction order across steps and - on this hardware - in lane order
     // inside a step.  That order is not promised, so it is CHECKED: keys are staged as 16-bit tile
@@ -742,11 +741,11 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
     // stable).  A violation is counted in *unordered; the host then repeats the suffix sort with the
     // peer-mask ranking.  Per key: one atomic, one random load, one 16-bit store and one random key
     // load instead of two atomics, two loads, two leader stores and the staging store.
-    constexpr bool OPT = (RANK2 == 5);
+    constexpr bool OPT = (RANK2 == 5);   // RANK2 == 0: peer-mask ranking (SALZ_SCATTER=1, and the fallback)
     uint16_t *sidx = (uint16_t *)maskA;     // OPT: [TILE] tile index of the key staged at each position
     // ---- consumer warps ----
     uint32_t *mycnt = wcnt + warp * 256;
-    uint32_t *myA = maskA + warp * 256, *myB = maskB + warp * 256;
+    uint32_t *myA = maskA + warp * 256;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t laneBit = 1u << lane;
 
@@ -775,82 +774,8 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
             const uint32_t idx = warp * (32 * ITEMS) + i * 32 + lane;
             key[i] = (idx < tl.valid) ? skeys[idx] : ~0ull;
         }
-        uint32_t lr[ITEMS / 2];       // RANK2 >= 2: warp-local ranks of a pair of keys, 16 bits each
-        if (RANK2 >= 2 && RANK2 <= 4) {
-            // ONE peer-mask step per key: the rank of a key among the keys of its warp with the
-            // same digit (running per-warp counter + lower peers) stays in a register, and the
-            // counters end up as the warp's digit histogram.  No separate counting atomics, and
-            // after the scan a key needs two independent loads and a store.
-#pragma unroll
-            for (int j = 0; j < ITEMS / 2; j++) {
-                const uint32_t d0 = (uint32_t)(key[2 * j] >> shift) & 255u, d1 = (uint32_t)(key[2 * j + 1] >> shift) & 255u;
-                const uint32_t p2 = d0 | (d1 << 8);
-                dd[j] = p2;
-                uint32_t r0, r1;
-                if (RANK2 != 4 && __reduce_and_sync(0xffffffffu, p2) == __reduce_or_sync(0xffffffffu, p2)) {
-                    const uint32_t c0 = mycnt[d0];
-                    const uint32_t c1 = mycnt[d1];
-                    r0 = c0 + lane;
-                    r1 = ((d0 == d1) ? c0 + 32 : c1) + lane;
-                    __syncwarp();
-                    if (lane == 0) {
-                        if (d0 == d1) mycnt[d0] = c0 + 64;
-                        else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
-                    }
-                } else if (RANK2 == 4) {
-                    // peer masks from 8 votes on the digit bits: no shared memory, no dependency
-                    // between the keys; what is left of the chain is the running counter
-                    uint32_t m0 = 0xffffffffu, m1 = 0xffffffffu;
-#pragma unroll
-                    for (int b = 0; b < 8; b++) {
-                        const bool b0 = (d0 >> b) & 1u, b1 = (d1 >> b) & 1u;
-                        const uint32_t v0 = __ballot_sync(0xffffffffu, b0), v1 = __ballot_sync(0xffffffffu, b1);
-                        m0 &= b0 ? v0 : ~v0;
-                        m1 &= b1 ? v1 : ~v1;
-                    }
-                    const uint32_t c0 = mycnt[d0];
-                    __syncwarp();
-                    r0 = c0 + __popc(m0 & lt_mask);
-                    if (lane == __ffs(m0) - 1) mycnt[d0] = c0 + __popc(m0);
-                    __syncwarp();
-                    const uint32_t c1 = mycnt[d1];
-                    __syncwarp();
-                    r1 = c1 + __popc(m1 & lt_mask);
-                    if (lane == __ffs(m1) - 1) mycnt[d1] = c1 + __popc(m1);
-                } else if (RANK2 == 3) {   // both keys of the pair in one step, two mask arrays
-                    atomicOr(&myA[d0], laneBit);
-                    atomicOr(&myB[d1], laneBit);
-                    __syncwarp();
-                    const uint32_t m0 = myA[d0], m1 = myB[d1];
-                    const uint32_t x = myA[d1];     // first keys with my second key's digit
-                    const uint32_t y = myB[d0];     // second keys with my first key's digit
-                    const uint32_t c0 = mycnt[d0], c1 = mycnt[d1];
-                    __syncwarp();
-                    r0 = c0 + __popc(m0 & lt_mask);
-                    r1 = c1 + __popc(x) + __popc(m1 & lt_mask);
-                    if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0) + __popc(y); }
-                    if (lane == __ffs(m1) - 1) { myB[d1] = 0; if (x == 0) mycnt[d1] = c1 + __popc(m1); }
-                } else {
-                    atomicOr(&myA[d0], laneBit);
-                    __syncwarp();
-                    const uint32_t m0 = myA[d0];
-                    const uint32_t c0 = mycnt[d0];
-                    __syncwarp();
-                    r0 = c0 + __popc(m0 & lt_mask);
-                    if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0); }
-                    __syncwarp();
-                    atomicOr(&myA[d1], laneBit);
-                    __syncwarp();
-                    const uint32_t m1 = myA[d1];
-                    const uint32_t c1 = mycnt[d1];
-                    __syncwarp();
-                    r1 = c1 + __popc(m1 & lt_mask);
-                    if (lane == __ffs(m1) - 1) { myA[d1] = 0; mycnt[d1] = c1 + __popc(m1); }
-                }
-                lr[j] = r0 | (r1 << 16);
-                __syncwarp();   // leaders' stores before the next step's atomics
-            }
-        } else if (OPT) {
+        uint32_t lr[ITEMS / 2];       // OPT: slots of a pair of keys, 16 bits each
+        if (OPT) {
             uint32_t o[ITEMS];   // all atomics of the tile are issued before the first result is needed
 #pragma unroll
             for (int j = 0; j < ITEMS / 2; j++) {
@@ -901,7 +826,6 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
 #pragma unroll
             for (int w = 0; w < WARPS; w++) {
                 const uint32_t c = wcnt[w * 256 + tid];
-                if (!FOLD) wcnt[w * 256 + tid] = sum;
                 sum += c;
             }
             total = sum;
@@ -924,30 +848,19 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
 #pragma unroll
             for (int w = 0; w < 7; w++) wb += (w < warp) ? scratch[w] : 0u;
             ex += wb;
-            dstart[tid] = ex;
-            if (FOLD) {
-                uint32_t run = ex;
+            // the counters become staging positions: digit start + the counts of the warps before
+            uint32_t run = ex;
 #pragma unroll
-                for (int w = 0; w < WARPS; w++) {
-                    const uint32_t c = wcnt[w * 256 + tid];
-                    wcnt[w * 256 + tid] = run;
-                    run += c;
-                }
+            for (int w = 0; w < WARPS; w++) {
+                const uint32_t c = wcnt[w * 256 + tid];
+                wcnt[w * 256 + tid] = run;
+                run += c;
             }
         }
         consumer_sync();
         PROF_MARK(4);
 
-        if (RANK2 >= 2 && RANK2 <= 4) {
-            // the counters now hold the exclusive prefix over the warps before mine
-#pragma unroll
-            for (int j = 0; j < ITEMS / 2; j++) {
-                const uint32_t d0 = dd[j] & 255u, d1 = dd[j] >> 8;
-                skeys[dstart[d0] + mycnt[d0] + (lr[j] & 0xffffu)] = key[2 * j];
-                skeys[dstart[d1] + mycnt[d1] + (lr[j] >> 16)] = key[2 * j + 1];
-            }
-            __syncwarp();
-        } else if (OPT) {
+        if (OPT) {
             // counters = first staging position of (warp, digit); the slot keeps the keys where they are
 #pragma unroll
             for (int j = 0; j < ITEMS / 2; j++) {
@@ -973,19 +886,6 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                     if (d0 == d1) mycnt[d0] = c0 + 64;
                     else { mycnt[d0] = c0 + 32; mycnt[d1] = c1 + 32; }
                 }
-            } else if (RANK2 == 1) {   // two keys per step, two mask arrays: the round trips of a step overlap
-                atomicOr(&myA[d0], laneBit);
-                atomicOr(&myB[d1], laneBit);
-                __syncwarp();
-                const uint32_t m0 = myA[d0], m1 = myB[d1];
-                const uint32_t x = myA[d1];     // first keys with my second key's digit
-                const uint32_t y = myB[d0];     // second keys with my first key's digit
-                const uint32_t c0 = mycnt[d0], c1 = mycnt[d1];
-                __syncwarp();
-                r0 = c0 + __popc(m0 & lt_mask);
-                r1 = c1 + __popc(x) + __popc(m1 & lt_mask);
-                if (lane == __ffs(m0) - 1) { myA[d0] = 0; mycnt[d0] = c0 + __popc(m0) + __popc(y); }
-                if (lane == __ffs(m1) - 1) { myB[d1] = 0; if (x == 0) mycnt[d1] = c1 + __popc(m1); }
             } else {
                 atomicOr(&myA[d0], laneBit);
                 __syncwarp();
@@ -1003,8 +903,8 @@ k_scatter_tma(uint64_t *buf0, uint64_t *buf1, ListView lv, PassPlan pp, const ui
                 r1 = c1 + __popc(m1 & lt_mask);
                 if (lane == __ffs(m1) - 1) { myA[d1] = 0; mycnt[d1] = c1 + __popc(m1); }
             }
-            skeys[(FOLD ? 0u : dstart[d0]) + r0] = key[2 * j];
-            skeys[(FOLD ? 0u : dstart[d1]) + r1] = key[2 * j + 1];
+            skeys[r0] = key[2 * j];
+            skeys[r1] = key[2 * j + 1];
             __syncwarp();   // leaders' stores before the next step's atomics
         }
         // the warp's counters are its own again: cleared for the next tile
@@ -1948,18 +1848,14 @@ int fetch_counters(SortCtx &s)
     return 0;
 }
 
-// SALZ_SCATTER: 1 = counts first, then ranking; 2 = the same with two keys per ranking step;
-// 3 = one ranking pass, warp-local ranks kept in registers; 4 = the same, two keys per step;
-// 5 = one ranking pass with peer masks from 8 votes on the digit bits (no mask arrays)
+// SALZ_SCATTER: 6 (default) = optimistic verified ranks; any other value > 0 = peer-mask ranking.
+// (Variants measured and dropped - two keys per step, one ranking pass with ranks in registers,
+// vote-built masks, a look-back warp - are in the history: DESIGN.md section 8.)
 void launch_scatter_tma(int mode, uint32_t grid, cudaStream_t st, uint64_t *a, uint64_t *b, const ListView &lv,
                         const PassPlan &pp, const uint32_t *digitBase, uint32_t *tileState, uint32_t *unordered)
 {
     switch (mode) {
     case 6: k_scatter_tma<5><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState, unordered); break;
-    case 2: k_scatter_tma<1><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState, unordered); break;
-    case 3: k_scatter_tma<2><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState, unordered); break;
-    case 4: k_scatter_tma<3><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState, unordered); break;
-    case 5: k_scatter_tma<4><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState, unordered); break;
     default: k_scatter_tma<0><<<grid, TTHREADS, SCATTER_TMA_SMEM, st>>>(a, b, lv, pp, digitBase, tileState, unordered); break;
     }
 }
@@ -2257,10 +2153,6 @@ int sa_init_device()
     CK(cudaFuncSetAttribute(k_local<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LTILE * 4));
     CK(cudaFuncSetAttribute(k_local<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LTILE * 4));
     CK(cudaFuncSetAttribute(k_scatter_tma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
-    CK(cudaFuncSetAttribute(k_scatter_tma<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     CK(cudaFuncSetAttribute(k_scatter_tma<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_TMA_SMEM));
     return 0;
 }
